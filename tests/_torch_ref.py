@@ -1,0 +1,46 @@
+"""Plain PyTorch restatement of the WKV6 recurrence used to pin the
+C oracle through torch.autograd.  Test helper only."""
+import torch
+
+
+def wkv6_recurrence(r, k, v, w, u, s0=None, rev=False):
+    """r,k,v,w [B,T,C]; u [H,N]; s0 [B,H,N,N] (value i, key j).  Returns y [B,T,C], S_T."""
+    B, T, C = r.shape
+    H, N = u.shape
+    rr, kk, vv, ww = (x.view(B, T, H, N) for x in (r, k, v, w))
+    S = torch.zeros(B, H, N, N, dtype=r.dtype) if s0 is None else s0
+    ys = [None] * T
+    order = range(T - 1, -1, -1) if rev else range(T)
+    for t in order:
+        rt, kt, vt = rr[:, t], kk[:, t], vv[:, t]                 # [B,H,N]
+        d = torch.exp(-torch.exp(ww[:, t]))                       # [B,H,N] over key j
+        kv = vt.unsqueeze(-1) * kt.unsqueeze(-2)                  # [B,H,i,j]
+        y = ((u.view(1, H, 1, N) * kv + S) * rt.unsqueeze(-2)).sum(-1)   # sum over j
+        ys[t] = y.reshape(B, C)
+        S = S * d.unsqueeze(-2) + kv
+    return torch.stack(ys, 1), S
+
+
+def make_inputs(B, T, H, N, seed=777, dtype=torch.float64, layer=0, n_layers=12, w_mode="init",
+                with_state=False):
+    """Synthetic op-level inputs of SURVEY.md section 8(d): r,k,v ~ N(0,1); w = time_decay init + 0.5 N(0,1)
+    (model.py:248-251) or the stress variant U(-8, 1.5); u = time_faaaa init (model.py:256-260)."""
+    C = H * N
+    g = torch.Generator().manual_seed(seed)
+    r, k, v, gy = (torch.randn(B, T, C, generator=g, dtype=torch.float64) for _ in range(4))
+    ratio = layer / max(n_layers - 1, 1)
+    n = torch.arange(C, dtype=torch.float64)
+    if w_mode == "init":
+        base = -6 + 5 * (n / max(C - 1, 1)) ** (0.7 + 1.3 * ratio)
+        w = base.view(1, 1, C) + 0.5 * torch.randn(B, T, C, generator=g, dtype=torch.float64)
+    elif w_mode == "stress":
+        w = torch.rand(B, T, C, generator=g, dtype=torch.float64) * 9.5 - 8.0
+    else:
+        raise ValueError(w_mode)
+    zig = ((n + 1) % 3 - 1) * 0.1
+    u = (ratio * (1 - n / max(C - 1, 1)) + zig).view(H, N)
+    out = dict(r=r, k=k, v=v, w=w, u=u, gy=gy)
+    if with_state:
+        out["s0"] = torch.randn(B, H, N, N, generator=g, dtype=torch.float64)
+        out["gsT"] = torch.randn(B, H, N, N, generator=g, dtype=torch.float64)
+    return {kk_: vv_.to(dtype) for kk_, vv_ in out.items()}
