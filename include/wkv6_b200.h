@@ -1,0 +1,111 @@
+/*
+ * wkv6_b200.h -- C ABI of libwkv6_b200.so: the B200 (sm_100a) implementation of the
+ * bidirectional RWKV-6 WKV6 scan (forward, reversed, backward pass).
+ *
+ * This is the drop-in boundary.  Every entry point replaces one host launcher of the
+ * reference (paths relative to the reference tree):
+ *
+ *   wkv6_b200_forward        <- cuda_forward / cuda_forward_fp32 / cuda_forward_fp64
+ *                               wenet/rwkv_v6/cuda/wkv6_cuda.cu:265-270, 282-287, 299-304
+ *                               (+ initial state: wkv6state_cuda.cu:7-65, 296-300)
+ *   wkv6_b200_backward       <- cuda_backward / cuda_backward_fp32 / cuda_backward_fp64
+ *                               wenet/rwkv_v6/cuda/wkv6_cuda.cu:272-280, 289-297, 306-314
+ *                               (+ gs: wkv6state_cuda.cu:68-293, 302-308)
+ *   wkv6_b200_bi_forward     <- the two cuda_forward launches (and the two torch.flip copies
+ *   wkv6_b200_bi_backward       around them) issued per layer by
+ *                               wenet/rwkv_v6/rwkv_wrapper_bidirectional.py:43-49
+ *   wkv6_b200_combine        <- `(x_att_forward + x_att_backward_fliped) / 2` + `.float()`
+ *                               wenet/rwkv_v6/rwkv_wrapper_bidirectional.py:48-56
+ *
+ * Conventions
+ *   - All tensor pointers are DEVICE pointers, contiguous, 16-byte aligned.
+ *     r,k,v,w,y,gy,gr,gk,gv,gw: [B,T,C] in `dtype`; u: [H,N] in `dtype`; gu: [B,C] in `dtype`
+ *     (per-batch partials, the caller sums over B exactly like model.py:151);
+ *     N = C / H must be 64.
+ *   - States are fp32: s0, sT, gs0, gsT: [B,H,N,N], index [b][h][i_value][j_key]
+ *     (layout of wkv6state_cuda.cu:15,24).  Any of them may be NULL
+ *     (s0 = NULL means S_0 = 0; gsT = NULL means no gradient flows into S_T).
+ *   - `reverse` != 0 runs the recurrence for t = T-1 .. 0 and writes every output at its
+ *     natural (un-flipped) position: identical to flip -> scan -> flip over the padded time
+ *     axis, without the copies.
+ *   - `stream` is a cudaStream_t (NULL = legacy default stream).  Calls are asynchronous.
+ *   - Return value: 0 on success, a negative WKV6_E_* code for rejected arguments,
+ *     a positive cudaError_t for CUDA failures.  wkv6_b200_last_error() gives the text.
+ *   - No CPU fallback exists: without a CUDA device every compute entry point fails.
+ */
+#ifndef WKV6_B200_H_
+#define WKV6_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WKV6_DTYPE_BF16 0
+#define WKV6_DTYPE_F32  1
+
+#define WKV6_E_BADARG   (-1)   /* NULL pointer, non-positive size, misaligned pointer          */
+#define WKV6_E_BADSHAPE (-2)   /* C != H*64                                                   */
+#define WKV6_E_BADDTYPE (-3)
+#define WKV6_E_NODRIVER (-4)   /* cuTensorMapEncodeTiled not obtainable from the driver       */
+#define WKV6_E_WORKSPACE (-5)  /* workspace too small                                         */
+
+/* flags of the bidirectional entry points */
+#define WKV6_BI_L2R      1     /* run the left-to-right direction (set "f")                   */
+#define WKV6_BI_R2L      2     /* run the right-to-left direction (set "b"), flip-free        */
+
+/* kernel selection for forward (bf16 only; f32 always uses the exact scan) */
+#define WKV6_ALGO_AUTO   0
+#define WKV6_ALGO_SCAN   1     /* fp32 recurrent scan on the FMA pipe (exact form)            */
+#define WKV6_ALGO_CHUNK  2     /* chunked dense-contraction form on tcgen05/TMEM              */
+
+int  wkv6_b200_abi_version(void);
+const char* wkv6_b200_last_error(void);
+/* Number of kernels this library has launched since load (the bench's gpu_launches). */
+long long wkv6_b200_launch_count(void);
+void wkv6_b200_set_algo(int algo);
+int  wkv6_b200_get_algo(void);
+
+int wkv6_b200_forward(int dtype, int B, int T, int C, int H,
+                      const void* r, const void* k, const void* v, const void* w, const void* u,
+                      const float* s0, void* y, float* sT, int reverse, void* stream);
+
+/* Bytes of scratch the backward entry points need (0 is possible). */
+size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections);
+
+int wkv6_b200_backward(int dtype, int B, int T, int C, int H,
+                       const void* r, const void* k, const void* v, const void* w, const void* u,
+                       const float* s0, const void* gy, const float* gsT,
+                       void* gr, void* gk, void* gv, void* gw, void* gu, float* gs0,
+                       int reverse, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Both directions in ONE launch per pass.  Set "f" scans t = 0..T-1, set "b" scans
+ * t = T-1..0 (flip-free).  `flags` selects which sets run (direction dropout): a set whose
+ * bit is clear is neither read nor written. */
+int wkv6_b200_bi_forward(int dtype, int B, int T, int C, int H,
+                         const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
+                         const float* s0_f, void* y_f, float* sT_f,
+                         const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
+                         const float* s0_b, void* y_b, float* sT_b,
+                         int flags, void* stream);
+
+int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
+                          const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
+                          const float* s0_f, const void* gy_f, const float* gsT_f,
+                          void* gr_f, void* gk_f, void* gv_f, void* gw_f, void* gu_f, float* gs0_f,
+                          const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
+                          const float* s0_b, const void* gy_b, const float* gsT_b,
+                          void* gr_b, void* gk_b, void* gv_b, void* gw_b, void* gu_b, float* gs0_b,
+                          int flags, void* workspace, size_t workspace_bytes, void* stream);
+
+/* out[i] = (a[i] + b[i]) * scale as fp32, a/b in `dtype`; b may be NULL (out = a*scale).
+ * n = number of elements. */
+int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float scale,
+                      float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WKV6_B200_H_ */

@@ -1,0 +1,13 @@
+"""paper_accurate_fast_cheap_b200 -- B200-native (sm_100a) bidirectional RWKV-6 WKV6 scan behind the
+reference's operator API (wenet/rwkv_v6).  See DESIGN.md / INTEGRATION.md."""
+from . import _lib
+from ._lib import Wkv6Error, launch_count, load_torch_ops, set_algo  # noqa: F401
+from .autograd import (BiWKV6, RUN_CUDA_RWKV6, RUN_CUDA_RWKV6_FP32, WKV6State, WKV_6, WKV_6_FP32,  # noqa: F401
+                       bi_wkv6, wkv6)
+from .ops import (bi_backward_raw, bi_forward_raw, combine, wkv6_backward_raw, wkv6_forward_raw)  # noqa: F401
+
+__all__ = [
+    "WKV_6", "WKV_6_FP32", "RUN_CUDA_RWKV6", "RUN_CUDA_RWKV6_FP32", "WKV6State", "BiWKV6", "wkv6", "bi_wkv6",
+    "wkv6_forward_raw", "wkv6_backward_raw", "bi_forward_raw", "bi_backward_raw", "combine",
+    "load_torch_ops", "launch_count", "set_algo", "Wkv6Error",
+]

@@ -1,0 +1,86 @@
+"""ctypes binding of libwkv6_b200.so (include/wkv6_b200.h).  Fails loudly: there is no CPU fallback."""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libwkv6_b200.so")
+TORCH_LIB_PATH = os.path.join(_HERE, "libwkv6_b200_torch.so")
+
+DTYPE_BF16, DTYPE_F32 = 0, 1
+BI_L2R, BI_R2L = 1, 2
+ALGO_AUTO, ALGO_SCAN, ALGO_CHUNK = 0, 1, 2
+
+# every symbol include/wkv6_b200.h declares
+SYMBOLS = (
+    "wkv6_b200_abi_version", "wkv6_b200_last_error", "wkv6_b200_launch_count", "wkv6_b200_set_algo",
+    "wkv6_b200_get_algo", "wkv6_b200_forward", "wkv6_b200_backward_workspace_bytes", "wkv6_b200_backward",
+    "wkv6_b200_bi_forward", "wkv6_b200_bi_backward", "wkv6_b200_combine",
+)
+
+_lib = None
+_vp, _i, _sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+
+
+class Wkv6Error(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    """Loads the CUDA library; raises if it has not been built (python -m paper_accurate_fast_cheap_b200.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise Wkv6Error(f"{LIB_PATH} is missing: build it with `python -m paper_accurate_fast_cheap_b200.build` "
+                        "(there is no CPU or PyTorch fallback for the WKV6 path)")
+    L = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
+    L.wkv6_b200_abi_version.restype = _i
+    L.wkv6_b200_last_error.restype = ctypes.c_char_p
+    L.wkv6_b200_launch_count.restype = ctypes.c_longlong
+    L.wkv6_b200_set_algo.argtypes = [_i]
+    L.wkv6_b200_get_algo.restype = _i
+    L.wkv6_b200_forward.argtypes = [_i] * 5 + [_vp] * 8 + [_i, _vp]
+    L.wkv6_b200_forward.restype = _i
+    L.wkv6_b200_backward_workspace_bytes.argtypes = [_i] * 6
+    L.wkv6_b200_backward_workspace_bytes.restype = _sz
+    L.wkv6_b200_backward.argtypes = [_i] * 5 + [_vp] * 14 + [_i, _vp, _sz, _vp]
+    L.wkv6_b200_backward.restype = _i
+    L.wkv6_b200_bi_forward.argtypes = [_i] * 5 + [_vp] * 16 + [_i, _vp]
+    L.wkv6_b200_bi_forward.restype = _i
+    L.wkv6_b200_bi_backward.argtypes = [_i] * 5 + [_vp] * 28 + [_i, _vp, _sz, _vp]
+    L.wkv6_b200_bi_backward.restype = _i
+    L.wkv6_b200_combine.argtypes = [_i, _sz, _vp, _vp, ctypes.c_float, _vp, _vp]
+    L.wkv6_b200_combine.restype = _i
+    _lib = L
+    return L
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise Wkv6Error(f"wkv6_b200 error {rc}: {lib().wkv6_b200_last_error().decode()}")
+
+
+def launch_count() -> int:
+    return int(lib().wkv6_b200_launch_count())
+
+
+def set_algo(algo: int) -> None:
+    lib().wkv6_b200_set_algo(int(algo))
+
+
+_torch_ops_loaded = False
+
+
+def load_torch_ops() -> None:
+    """Registers torch.ops.wkv6.{forward,backward}[_fp32|_fp64] (the reference's dispatcher namespace)."""
+    global _torch_ops_loaded
+    if _torch_ops_loaded:
+        return
+    import torch
+    lib()
+    if not os.path.exists(TORCH_LIB_PATH):
+        raise Wkv6Error(f"{TORCH_LIB_PATH} is missing: build it with `python -m paper_accurate_fast_cheap_b200.build`")
+    torch.ops.load_library(TORCH_LIB_PATH)
+    _torch_ops_loaded = True

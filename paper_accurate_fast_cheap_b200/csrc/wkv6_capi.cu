@@ -1,0 +1,260 @@
+// wkv6_capi.cu -- the C ABI of include/wkv6_b200.h: argument validation, TMA tensor-map encoding,
+// kernel selection and launch.  No torch types, no allocation, no synchronisation.
+#include "../../include/wkv6_b200.h"
+#include "wkv6_scan.cuh"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+namespace wkv6 {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_algo{WKV6_ALGO_AUTO};
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+static int cuda_fail(int e, const char* where) {
+    if (e == 0) return 0;
+    snprintf(g_err, sizeof(g_err), "%s: %s (%d)", where, cudaGetErrorString((cudaError_t)e), e);
+    return e > 0 ? e : -e;
+}
+
+typedef CUresult (*encode_fn_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_fn_t get_encode() {
+    static encode_fn_t fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<encode_fn_t>(p);
+    });
+    return fn;
+}
+
+// 3-D view [B][T][C] of a contiguous tensor, box = [1][rows][64 channels]
+static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, int C, int rows) {
+    encode_fn_t enc = get_encode();
+    if (!enc) return fail(WKV6_E_NODRIVER, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    const size_t es = dtype == WKV6_DTYPE_BF16 ? 2 : 4;
+    const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)T, (cuuint64_t)B};
+    const cuuint64_t strides[2] = {(cuuint64_t)C * es, (cuuint64_t)T * C * es};
+    const cuuint32_t box[3] = {64u, (cuuint32_t)rows, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    const CUresult r = enc(m, dtype == WKV6_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                           3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(WKV6_E_BADARG, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return 0;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+static int check_common(int dtype, int B, int T, int C, int H) {
+    if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
+    if (B < 0 || T < 0 || C <= 0 || H <= 0) return fail(WKV6_E_BADARG, "bad sizes B=%d T=%d C=%d H=%d", B, T, C, H);
+    if (C != H * N) return fail(WKV6_E_BADSHAPE, "C (%d) must equal H (%d) * 64: head size 64 only", C, H);
+    return 0;
+}
+
+struct FwdSet {
+    const void *r, *k, *v, *w, *u;
+    const float* s0;
+    void* y;
+    float* sT;
+};
+struct BwdSet {
+    const void *r, *k, *v, *w, *u;
+    const float* s0;
+    const void* gy;
+    const float* gsT;
+    void *gr, *gk, *gv, *gw, *gu;
+    float* gs0;
+};
+
+static bool use_chunk(int dtype, int T) {
+    const int a = g_algo.load(std::memory_order_relaxed);
+    if (dtype != WKV6_DTYPE_BF16) return false;
+    if (a == WKV6_ALGO_CHUNK) return true;
+    return false;   // AUTO: exact scan until the chunk kernel is validated
+}
+
+static int fill_fwd(DirArgs& d, int dtype, int B, int T, int C, const FwdSet& s, int reverse, int rows, bool want_ymap) {
+    const void* ptrs[5] = {s.r, s.k, s.v, s.w, s.y};
+    for (const void* q : ptrs)
+        if (!q || !aligned16(q)) return fail(WKV6_E_BADARG, "forward: NULL or misaligned tensor pointer");
+    if (!s.u) return fail(WKV6_E_BADARG, "forward: u is NULL");
+    if ((s.s0 && !aligned16(s.s0)) || (s.sT && !aligned16(s.sT))) return fail(WKV6_E_BADARG, "forward: misaligned state");
+    int e;
+    if ((e = make_map(&d.mr, dtype, s.r, B, T, C, rows))) return e;
+    if ((e = make_map(&d.mk, dtype, s.k, B, T, C, rows))) return e;
+    if ((e = make_map(&d.mv, dtype, s.v, B, T, C, rows))) return e;
+    if ((e = make_map(&d.mw, dtype, s.w, B, T, C, rows))) return e;
+    if (want_ymap && (e = make_map(&d.my, dtype, s.y, B, T, C, rows))) return e;
+    d.u = s.u; d.s0 = s.s0; d.sT = s.sT; d.y = s.y;
+    d.reverse = reverse;
+    return 0;
+}
+
+static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets, const int* reverse, int nset, void* stream) {
+    int e = check_common(dtype, B, T, C, H);
+    if (e) return e;
+    if (nset == 0 || B == 0) return 0;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.C = C; p.H = H; p.ndir = nset;
+    if (T == 0) {   // empty sequence: S_T = S_0
+        for (int i = 0; i < nset; i++)
+            if (sets[i].sT) {
+                const size_t bytes = (size_t)B * H * N * N * sizeof(float);
+                cudaError_t ce = sets[i].s0 ? cudaMemcpyAsync(sets[i].sT, sets[i].s0, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream)
+                                            : cudaMemsetAsync(sets[i].sT, 0, bytes, (cudaStream_t)stream);
+                if (ce != cudaSuccess) return cuda_fail((int)ce, "forward(T=0)");
+            }
+        return 0;
+    }
+    const bool chunk = use_chunk(dtype, T);
+    for (int i = 0; i < nset; i++)
+        if ((e = fill_fwd(p.d[i], dtype, B, T, C, sets[i], reverse[i], chunk ? 64 : TT, chunk))) return e;
+    e = chunk ? launch_fwd_chunk(p, (cudaStream_t)stream) : launch_fwd_scan(dtype, p, (cudaStream_t)stream);
+    return cuda_fail(e, "wkv6 forward launch");
+}
+
+static int run_backward(int dtype, int B, int T, int C, int H, const BwdSet* sets, const int* reverse, int nset,
+                        void* ws, size_t ws_bytes, void* stream) {
+    int e = check_common(dtype, B, T, C, H);
+    if (e) return e;
+    if (nset == 0 || B == 0) return 0;
+    const size_t es = dtype == WKV6_DTYPE_BF16 ? 2 : 4;
+    if (T == 0) {   // no steps: all sequence gradients are empty, gu = 0, gs0 = gsT
+        for (int i = 0; i < nset; i++) {
+            cudaError_t ce = cudaMemsetAsync(sets[i].gu, 0, (size_t)B * C * es, (cudaStream_t)stream);
+            if (ce == cudaSuccess && sets[i].gs0) {
+                const size_t bytes = (size_t)B * H * N * N * sizeof(float);
+                ce = sets[i].gsT ? cudaMemcpyAsync(sets[i].gs0, sets[i].gsT, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream)
+                                 : cudaMemsetAsync(sets[i].gs0, 0, bytes, (cudaStream_t)stream);
+            }
+            if (ce != cudaSuccess) return cuda_fail((int)ce, "backward(T=0)");
+        }
+        return 0;
+    }
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.C = C; p.H = H; p.ndir = nset;
+    const size_t per_dir = (size_t)B * H * N * sizeof(float);
+    for (int i = 0; i < nset; i++) {
+        const BwdSet& s = sets[i];
+        DirArgs& d = p.d[i];
+        const void* ptrs[10] = {s.r, s.k, s.v, s.w, s.gy, s.gr, s.gk, s.gv, s.gw, s.gu};
+        for (const void* q : ptrs)
+            if (!q || !aligned16(q)) return fail(WKV6_E_BADARG, "backward: NULL or misaligned tensor pointer");
+        if (!s.u) return fail(WKV6_E_BADARG, "backward: u is NULL");
+        if ((e = make_map(&d.mr, dtype, s.r, B, T, C, TT))) return e;
+        if ((e = make_map(&d.mk, dtype, s.k, B, T, C, TT))) return e;
+        if ((e = make_map(&d.mv, dtype, s.v, B, T, C, TT))) return e;
+        if ((e = make_map(&d.mw, dtype, s.w, B, T, C, TT))) return e;
+        if ((e = make_map(&d.mg, dtype, s.gy, B, T, C, TT))) return e;
+        if ((e = make_map(&d.mq, dtype, s.gr, B, T, C, TT))) return e;
+        d.u = s.u; d.s0 = s.s0; d.gsT = s.gsT; d.gs0 = s.gs0;
+        d.gr = s.gr; d.gk = s.gk; d.gv = s.gv; d.gw = s.gw; d.gu = s.gu;
+        d.reverse = reverse[i];
+        d.hT = nullptr;
+        if (s.gsT) {
+            if (!ws || ws_bytes < per_dir * (size_t)nset || !aligned16(ws))
+                return fail(WKV6_E_WORKSPACE, "backward with gsT needs %zu workspace bytes (wkv6_b200_backward_workspace_bytes)",
+                            per_dir * (size_t)nset);
+            d.hT = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + per_dir * i);
+        }
+    }
+    e = launch_bwd_scan(dtype, p, (cudaStream_t)stream);
+    return cuda_fail(e, "wkv6 backward launch");
+}
+
+}  // namespace wkv6
+
+using namespace wkv6;
+
+extern "C" {
+
+int wkv6_b200_abi_version(void) { return 1; }
+const char* wkv6_b200_last_error(void) { return g_err; }
+long long wkv6_b200_launch_count(void) { return g_launches.load(); }
+void wkv6_b200_set_algo(int algo) { g_algo.store(algo); }
+int wkv6_b200_get_algo(void) { return g_algo.load(); }
+
+int wkv6_b200_forward(int dtype, int B, int T, int C, int H, const void* r, const void* k, const void* v, const void* w,
+                      const void* u, const float* s0, void* y, float* sT, int reverse, void* stream) {
+    const FwdSet s = {r, k, v, w, u, s0, y, sT};
+    const int rv = reverse != 0;
+    return run_forward(dtype, B, T, C, H, &s, &rv, 1, stream);
+}
+
+size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
+    (void)dtype; (void)T; (void)C;
+    if (B <= 0 || H <= 0 || ndirections <= 0) return 0;
+    return (size_t)ndirections * B * H * N * sizeof(float);
+}
+
+int wkv6_b200_backward(int dtype, int B, int T, int C, int H, const void* r, const void* k, const void* v, const void* w,
+                       const void* u, const float* s0, const void* gy, const float* gsT, void* gr, void* gk, void* gv,
+                       void* gw, void* gu, float* gs0, int reverse, void* workspace, size_t workspace_bytes, void* stream) {
+    const BwdSet s = {r, k, v, w, u, s0, gy, gsT, gr, gk, gv, gw, gu, gs0};
+    const int rv = reverse != 0;
+    return run_backward(dtype, B, T, C, H, &s, &rv, 1, workspace, workspace_bytes, stream);
+}
+
+int wkv6_b200_bi_forward(int dtype, int B, int T, int C, int H,
+                         const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
+                         const float* s0_f, void* y_f, float* sT_f,
+                         const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
+                         const float* s0_b, void* y_b, float* sT_b, int flags, void* stream) {
+    FwdSet sets[2];
+    int rv[2];
+    int n = 0;
+    if (flags & WKV6_BI_L2R) { sets[n] = {r_f, k_f, v_f, w_f, u_f, s0_f, y_f, sT_f}; rv[n++] = 0; }
+    if (flags & WKV6_BI_R2L) { sets[n] = {r_b, k_b, v_b, w_b, u_b, s0_b, y_b, sT_b}; rv[n++] = 1; }
+    return run_forward(dtype, B, T, C, H, sets, rv, n, stream);
+}
+
+int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
+                          const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
+                          const float* s0_f, const void* gy_f, const float* gsT_f,
+                          void* gr_f, void* gk_f, void* gv_f, void* gw_f, void* gu_f, float* gs0_f,
+                          const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
+                          const float* s0_b, const void* gy_b, const float* gsT_b,
+                          void* gr_b, void* gk_b, void* gv_b, void* gw_b, void* gu_b, float* gs0_b,
+                          int flags, void* workspace, size_t workspace_bytes, void* stream) {
+    BwdSet sets[2];
+    int rv[2];
+    int n = 0;
+    if (flags & WKV6_BI_L2R) { sets[n] = {r_f, k_f, v_f, w_f, u_f, s0_f, gy_f, gsT_f, gr_f, gk_f, gv_f, gw_f, gu_f, gs0_f}; rv[n++] = 0; }
+    if (flags & WKV6_BI_R2L) { sets[n] = {r_b, k_b, v_b, w_b, u_b, s0_b, gy_b, gsT_b, gr_b, gk_b, gv_b, gw_b, gu_b, gs0_b}; rv[n++] = 1; }
+    return run_backward(dtype, B, T, C, H, sets, rv, n, workspace, workspace_bytes, stream);
+}
+
+int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float scale, float* out, void* stream) {
+    if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
+    if (n == 0) return 0;
+    if (!a || !out || !aligned16(a) || !aligned16(out) || (b && !aligned16(b)) || (n % 8))
+        return fail(WKV6_E_BADARG, "combine: NULL/misaligned pointer or n %% 8 != 0");
+    return cuda_fail(launch_combine(dtype, n, a, b, scale, out, (cudaStream_t)stream), "wkv6 combine launch");
+}
+
+}  // extern "C"

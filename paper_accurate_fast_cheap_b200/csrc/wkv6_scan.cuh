@@ -1,0 +1,41 @@
+// wkv6_scan.cuh -- parameter blocks shared by the kernels and the C ABI (wkv6_capi.cu).
+#pragma once
+#include "wkv6_common.cuh"
+
+namespace wkv6 {
+
+constexpr int TT = 16;    // time steps per TMA tile of the exact scan kernels
+constexpr int NT = 128;   // threads per CTA of the exact scan kernels (one CTA per (direction, b, h))
+
+// One direction ("set") of a call.  Tensor maps are 3-D views [B][T][C] with box [1][TT][64].
+struct alignas(64) DirArgs {
+    CUtensorMap mr, mk, mv, mw, mg, mq;   // r, k, v, w, gy, gr(as input of pass B)
+    CUtensorMap my;                       // y (TMA store; chunk kernel only)
+    const void* u;                        // [H,64] io dtype
+    const float* s0;                      // [B,H,64,64] or null
+    float* sT;                            // [B,H,64,64] or null
+    void* y;                              // [B,T,C]
+    const float* gsT;                     // bwd: gradient into S_T or null
+    float* gs0;                           // bwd: gradient w.r.t. S_0 or null
+    void *gr, *gk, *gv, *gw;              // [B,T,C]
+    void* gu;                             // [B,C]
+    float* hT;                            // workspace [B*H*64]: sum_i S_T[i][j]*gsT[i][j]  (pass A -> pass B)
+    int reverse;                          // scan t = T-1..0
+    int pad_;
+};
+
+struct Params {
+    DirArgs d[2];
+    int B, T, C, H;
+    int ndir;
+};
+
+// launchers (wkv6_scan.cu / wkv6_chunk.cu); return cudaError_t as int
+int launch_fwd_scan(int dtype, const Params& p, cudaStream_t st);
+int launch_bwd_scan(int dtype, const Params& p, cudaStream_t st);
+int launch_fwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05
+int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, float* out, cudaStream_t st);
+
+void count_launch(int n);
+
+}  // namespace wkv6

@@ -1,0 +1,153 @@
+"""Host side of the WKV6 operator: the reference's autograd.Function API on top of the C ABI.
+
+Mirrors wenet/rwkv_v6/src/model.py:108-214 (WKV_6, WKV_6_FP32, RUN_CUDA_RWKV6[_FP32]): same names, argument
+order, dtype/contiguity asserts and the same `gu.sum(0).view(H, N)` post-op.  Adds the superset the north star
+asks for: initial state in, final state out, reversed (flip-free) direction, and both directions in one launch
+with direction-dropout flags (`bi_wkv6`).  PyTorch is used for memory and streams only; all arithmetic happens in
+libwkv6_b200.so.  There is no CPU path: CPU tensors raise.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+HEAD_SIZE = 64
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return _lib.DTYPE_BF16
+    if t.dtype == torch.float32:
+        return _lib.DTYPE_F32
+    raise TypeError(f"wkv6: unsupported dtype {t.dtype} (bfloat16 and float32 only)")
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream(t: torch.Tensor):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _check_inputs(r, k, v, w, u, extra=()):
+    assert r.is_cuda, "wkv6: CUDA tensors only (no CPU fallback in this build)"
+    B, T, C = r.size()
+    assert C % HEAD_SIZE == 0
+    H = C // HEAD_SIZE
+    for t in (r, k, v, w) + tuple(extra):
+        assert t.dtype == r.dtype and t.device == r.device
+        assert t.is_contiguous()
+        assert t.size() == r.size()
+    assert u.dtype == r.dtype and u.is_contiguous() and u.numel() == C
+    return B, T, C, H
+
+
+def _check_state(s, B, H, dev):
+    if s is not None:
+        assert s.dtype == torch.float32 and s.is_contiguous() and s.device == dev
+        assert tuple(s.shape) == (B, H, HEAD_SIZE, HEAD_SIZE)
+
+
+# --------------------------------------------------------------------------------------------------
+# raw (no autograd) calls into the C ABI
+# --------------------------------------------------------------------------------------------------
+def wkv6_forward_raw(r, k, v, w, u, s0=None, reverse=False, want_state=False):
+    B, T, C, H = _check_inputs(r, k, v, w, u)
+    _check_state(s0, B, H, r.device)
+    y = torch.empty_like(r)
+    sT = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_state else None
+    with torch.cuda.device(r.device):
+        _lib.check(_lib.lib().wkv6_b200_forward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u),
+                                                _p(s0), _p(y), _p(sT), int(bool(reverse)), _stream(r)))
+    return y, sT
+
+
+def wkv6_backward_raw(r, k, v, w, u, gy, s0=None, gsT=None, reverse=False, want_gs0=False):
+    """Returns gr, gk, gv, gw [B,T,C], gu [B,C] (per-batch partials, like the reference), gs0 or None."""
+    B, T, C, H = _check_inputs(r, k, v, w, u, extra=(gy,))
+    _check_state(s0, B, H, r.device)
+    _check_state(gsT, B, H, r.device)
+    gr, gk, gv, gw = (torch.empty_like(r) for _ in range(4))
+    gu = torch.empty((B, C), device=r.device, dtype=r.dtype)
+    gs0 = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_gs0 else None
+    L = _lib.lib()
+    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, 1) if gsT is not None else 0
+    ws = torch.empty(ws_bytes, device=r.device, dtype=torch.uint8) if ws_bytes else None
+    with torch.cuda.device(r.device):
+        _lib.check(L.wkv6_b200_backward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u), _p(s0),
+                                        _p(gy), _p(gsT), _p(gr), _p(gk), _p(gv), _p(gw), _p(gu), _p(gs0),
+                                        int(bool(reverse)), _p(ws), ws_bytes, _stream(r)))
+    return gr, gk, gv, gw, gu, gs0
+
+
+def bi_forward_raw(f, b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, want_state=False):
+    """f, b: (r, k, v, w, u) of the L2R / R2L direction.  One launch.  Returns (y_f, y_b, sT_f, sT_b);
+    outputs of a direction whose flag bit is clear are None."""
+    ref = f if (flags & _lib.BI_L2R) else b
+    B, T, C, H = _check_inputs(*ref)
+    run_f, run_b = bool(flags & _lib.BI_L2R), bool(flags & _lib.BI_R2L)
+    if run_f and run_b:
+        _check_inputs(*b)
+        assert b[0].size() == f[0].size() and b[0].dtype == f[0].dtype
+    dev, dt = ref[0].device, ref[0].dtype
+    mk = lambda: torch.empty((B, T, C), device=dev, dtype=dt)
+    mks = lambda: torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=dev, dtype=torch.float32)
+    y_f = mk() if run_f else None
+    y_b = mk() if run_b else None
+    sT_f = mks() if (run_f and want_state) else None
+    sT_b = mks() if (run_b and want_state) else None
+    none5 = (None,) * 5
+    fa = tuple(_p(t) for t in f) if run_f else none5
+    ba = tuple(_p(t) for t in b) if run_b else none5
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().wkv6_b200_bi_forward(_dtype_code(ref[0]), B, T, C, H,
+                                                   *fa, _p(s0_f), _p(y_f), _p(sT_f),
+                                                   *ba, _p(s0_b), _p(y_b), _p(sT_b), int(flags), _stream(ref[0])))
+    return y_f, y_b, sT_f, sT_b
+
+
+def bi_backward_raw(f, b, gy_f, gy_b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, gsT_f=None, gsT_b=None,
+                    want_gs0=False):
+    """Backward of bi_forward_raw: two launches (sweep A, sweep B) covering both directions.
+    Returns two tuples (gr, gk, gv, gw, gu[B,C], gs0) -- None for a direction that did not run."""
+    run_f, run_b = bool(flags & _lib.BI_L2R), bool(flags & _lib.BI_R2L)
+    ref = f if run_f else b
+    B, T, C, H = _check_inputs(*ref)
+    dev, dt = ref[0].device, ref[0].dtype
+
+    def outs(run):
+        if not run:
+            return (None,) * 6
+        o = [torch.empty((B, T, C), device=dev, dtype=dt) for _ in range(4)]
+        o.append(torch.empty((B, C), device=dev, dtype=dt))
+        o.append(torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=dev, dtype=torch.float32) if want_gs0 else None)
+        return tuple(o)
+
+    of, ob = outs(run_f), outs(run_b)
+    L = _lib.lib()
+    need_ws = (gsT_f is not None) or (gsT_b is not None)
+    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(ref[0]), B, T, C, H, 2) if need_ws else 0
+    ws = torch.empty(ws_bytes, device=dev, dtype=torch.uint8) if ws_bytes else None
+    none5 = (None,) * 5
+    fa = tuple(_p(t) for t in f) if run_f else none5
+    ba = tuple(_p(t) for t in b) if run_b else none5
+    with torch.cuda.device(dev):
+        _lib.check(L.wkv6_b200_bi_backward(
+            _dtype_code(ref[0]), B, T, C, H,
+            *fa, _p(s0_f), _p(gy_f), _p(gsT_f), *[_p(t) for t in of],
+            *ba, _p(s0_b), _p(gy_b), _p(gsT_b), *[_p(t) for t in ob],
+            int(flags), _p(ws), ws_bytes, _stream(ref[0])))
+    return of, ob
+
+
+def combine(a: torch.Tensor, b: Optional[torch.Tensor], scale: float = 0.5) -> torch.Tensor:
+    """(a + b) * scale as float32 in one pass (rwkv_wrapper_bidirectional.py:48-56)."""
+    assert a.is_cuda and a.is_contiguous() and (b is None or (b.is_contiguous() and b.shape == a.shape and b.dtype == a.dtype))
+    out = torch.empty(a.shape, device=a.device, dtype=torch.float32)
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.lib().wkv6_b200_combine(_dtype_code(a), a.numel(), _p(a), _p(b), float(scale), _p(out), _stream(a)))
+    return out
