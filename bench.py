@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""bench.py -- encoder frames/s of the bidirectional WKV6 hot path on N B200s (one process per GPU).
+
+Workload (BASELINE.json configs[1]): full bidirectional RWKV-6 encoder's WKV6 work -- 12 blocks, d_model 512,
+8 heads x 64, bf16, B=16 x T=750 subsampled frames (30 s), inference (forward, both directions, one launch per
+block).  One "step" = the 12 bidirectional scans of one batch.  N>1: every rank scans its own batch of 16
+utterances (sharded by utterance, no collective) -> weak scaling.  `--mode train` times fwd+bwd instead.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--mode infer|train]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+CFG = dict(layers=12, C=512, H=8, B=16, T=750)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"])
+    ap.add_argument("--algo", default="auto", choices=["auto", "scan", "chunk"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons with nvidia-smi while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_sample(threads=None):
+    """The oracle port timed on the host cores: ONE of the 12 blocks, both directions, full B x T."""
+    import torch
+    import oracle
+    from _torch_ref import make_inputs
+    if threads:
+        oracle.set_threads(threads)
+    c = CFG
+    sets = [make_inputs(c["B"], c["T"], c["H"], 64, seed=s, dtype=torch.float32) for s in (11, 12)]
+    oracle.fwd(sets[0]["r"][:1], sets[0]["k"][:1], sets[0]["v"][:1], sets[0]["w"][:1], sets[0]["u"])   # warm
+    t0 = time.perf_counter()
+    for s, rev in zip(sets, (False, True)):
+        oracle.fwd(s["r"], s["k"], s["v"], s["w"], s["u"], rev=rev, prec="f32")
+    dt = time.perf_counter() - t0
+    fps = c["B"] * c["T"] / (dt * c["layers"])
+    return fps, dt, oracle.num_threads()
+
+
+def config_dict(args, extra=None):
+    c = CFG
+    d = {"workload": f"configs[1]: bi-WKV6 of a {c['layers']}-block RWKV-6 encoder, d_model={c['C']}, {c['H']} heads x 64, "
+                     f"B={c['B']} x T={c['T']} per GPU, {'fwd (inference)' if args.mode == 'infer' else 'fwd+bwd (training)'}",
+         "layers": c["layers"], "B_per_gpu": c["B"], "T": c["T"], "C": c["C"], "H": c["H"], "mode": args.mode,
+         "parallelism": f"utterance-sharded x{args.gpus}, no collective",
+         "l2": "inputs (1.18 GB per step) exceed the 126 MB L2; every block reads its own tensors"}
+    if extra:
+        d.update(extra)
+    return d
+
+
+def run_reference(args):
+    """Reference arm: the reference has no CPU WKV6 (model.py:105-106 is CUDA-only), so this times the oracle
+    port of its kernels on all host cores.  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    oracle.build()
+    vals = []
+    for i in range(args.warmup + args.steps):
+        fps, dt, th = cpu_sample()
+        if i >= args.warmup:
+            vals.append((fps, dt))
+    fps = sum(v[0] for v in vals) / len(vals)
+    ms = 1e3 * sum(v[1] for v in vals) / len(vals) * CFG["layers"]
+    sample = "1 of 12 blocks, both directions, full B=16 x T=750, fp32 oracle port (OpenMP over batch x head); x12 extrapolated"
+    line = {"impl": "reference", "metric": "encoder frames/s (bi-WKV6)", "value": fps, "unit": "frames/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args),
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": th, "kind": "port", "sample": sample},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def make_layer_inputs(torch, dev, layer, dtype, train, pinned=False):
+    """Synthetic op-level inputs of SURVEY 8(d) for one block: L2R set and R2L set."""
+    c = CFG
+    g = torch.Generator(device="cpu").manual_seed(777 + layer)
+    C, H, B, T, L = c["C"], c["H"], c["B"], c["T"], c["layers"]
+    ratio = layer / (L - 1)
+    n = torch.arange(C, dtype=torch.float32)
+    base = (-6 + 5 * (n / (C - 1)) ** (0.7 + 1.3 * ratio)).view(1, 1, C)
+    u = (ratio * (1 - n / (C - 1)) + ((n + 1) % 3 - 1) * 0.1).view(H, 64)
+    sets = []
+    for _ in range(2):
+        t = [torch.randn(B, T, C, generator=g) for _ in range(3)]
+        t.append(base + 0.5 * torch.randn(B, T, C, generator=g))
+        t.append(u.clone())
+        if train:
+            t.append(torch.randn(B, T, C, generator=g))
+        t = [x.to(dtype).contiguous() for x in t]
+        sets.append([x.pin_memory() for x in t] if pinned else [x.to(dev) for x in t])
+    return sets
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import paper_accurate_fast_cheap_b200 as pk
+    from paper_accurate_fast_cheap_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    pk.set_algo({"auto": _lib.ALGO_AUTO, "scan": _lib.ALGO_SCAN, "chunk": _lib.ALGO_CHUNK}[args.algo])
+    L = _lib.lib()
+    c = CFG
+    B, T, C, H, NL = c["B"], c["T"], c["C"], c["H"], c["layers"]
+    train = args.mode == "train"
+    dt = torch.bfloat16
+    layers = [make_layer_inputs(torch, dev, l, dt, train) for l in range(NL)]
+    mk = lambda: torch.empty(B, T, C, device=dev, dtype=dt)
+    outs = [[mk(), mk()] for _ in range(NL)]
+    gouts = [[[mk() for _ in range(4)] + [torch.empty(B, C, device=dev, dtype=dt)] for _ in range(2)] for _ in range(NL)] if train else None
+    stream = torch.cuda.current_stream().cuda_stream
+    flags = _lib.BI_L2R | _lib.BI_R2L
+    p = lambda t: t.data_ptr()
+
+    def fwd_layer(l, ins=None, ys=None):
+        f, b = ins or layers[l]
+        yf, yb = ys or outs[l]
+        _lib.check(L.wkv6_b200_bi_forward(0, B, T, C, H, p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(yf), None,
+                                          p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(yb), None, flags, stream))
+
+    def bwd_layer(l):
+        f, b = layers[l]
+        gf, gb = gouts[l]
+        _lib.check(L.wkv6_b200_bi_backward(
+            0, B, T, C, H,
+            p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(f[5]), None, *[p(x) for x in gf], None,
+            p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(b[5]), None, *[p(x) for x in gb], None,
+            flags, None, 0, stream))
+
+    ev_pairs = []
+
+    def step(record=False):
+        for l in range(NL):
+            if record:
+                e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+                e0.record()
+            fwd_layer(l)
+            if record:
+                e1.record(); ev_pairs.append((e0, e1))
+        if train:
+            for l in reversed(range(NL)):
+                bwd_layer(l)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    n0 = pk.launch_count()
+    sampler = ClockSampler(local); sampler.start()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(args.steps):
+        step(record=True)
+    t1.record()
+    barrier()
+    sampler.stop_flag = True
+    launches = pk.launch_count() - n0
+    ms_total = t0.elapsed_time(t1)
+    tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    value = world * B * T / (ms_step * 1e-3)
+    kern_ms = sum(a.elapsed_time(b) for a, b in ev_pairs) / len(ev_pairs)
+    alg_bytes = 2 * 5 * B * T * C * 2                     # both directions: read r,k,v,w + write y, bf16
+    pk_, how = peaks()
+    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": "wkv6 bidirectional forward (one launch per block)", "achieved": achieved,
+            "peak": pk_["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk_["hbm_gbs"], "peak_source": how,
+            "traffic": None, "alg_bytes_per_launch": alg_bytes, "kernel_ms": kern_ms}
+
+    # ---- end to end: pinned host inputs -> H2D -> op -> D2H of y, every step, through the public API
+    e2e = None
+    if not args.no_e2e and not train:
+        host = [make_layer_inputs(torch, dev, l, dt, False, pinned=True) for l in range(2)]   # 2 distinct blocks, reused
+        stage = [[[torch.empty_like(x, device=dev) for x in s] for s in host[0]] for _ in range(2)]
+        ystage = [[mk(), mk()] for _ in range(2)]
+        yhost = [[torch.empty(B, T, C, dtype=dt).pin_memory() for _ in range(2)] for _ in range(2)]
+        h2d = sum(x.numel() * x.element_size() for s in host[0] for x in s) * NL
+        d2h = 2 * B * T * C * 2 * NL
+
+        def e2e_step():
+            for l in range(NL):
+                src, dst = host[l & 1], stage[l & 1]
+                for s_h, s_d in zip(src, dst):
+                    for xh, xd in zip(s_h, s_d):
+                        xd.copy_(xh, non_blocking=True)
+                fwd_layer(l, ins=dst, ys=ystage[l & 1])
+                for yh, yd in zip(yhost[l & 1], ystage[l & 1]):
+                    yh.copy_(yd, non_blocking=True)
+
+        e2e_steps = max(2, min(args.steps, 5))
+        e2e_step(); barrier()
+        a = torch.cuda.Event(enable_timing=True); b_ = torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        b_.record(); barrier()
+        te = torch.tensor([a.elapsed_time(b_)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * B * T / (float(te.item()) / e2e_steps * 1e-3), "unit": "frames/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps}
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            fps, secs, th = cpu_sample()
+            cpu = {"value": fps, "unit": "frames/s", "cores": th, "kind": "port",
+                   "sample": f"1 of 12 blocks, both directions, full B=16 x T=750 ({secs:.2f} s of CPU work), x12 extrapolated"}
+        line = {"metric": "encoder frames/s (bi-WKV6)", "value": value, "unit": "frames/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": config_dict(args, {"algo": args.algo}), "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
+                "gpu_launches": launches, "clocks": sampler.summary()}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
