@@ -181,6 +181,9 @@ def run_b200(args):
         _lib.check(L.wkv6_b200_bi_forward(0, B, T, C, H, p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(yf), None,
                                           p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(yb), None, flags, stream))
 
+    ws_bytes = L.wkv6_b200_backward_workspace_bytes(0, B, T, C, H, 2) if train else 0
+    ws = torch.empty(max(ws_bytes, 16), device=dev, dtype=torch.uint8)
+
     def bwd_layer(l):
         f, b = layers[l]
         gf, gb = gouts[l]
@@ -188,7 +191,7 @@ def run_b200(args):
             0, B, T, C, H,
             p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(f[5]), None, *[p(x) for x in gf], None,
             p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(b[5]), None, *[p(x) for x in gb], None,
-            flags, None, 0, stream))
+            flags, p(ws), ws_bytes, stream))
 
     ev_pairs = []
 

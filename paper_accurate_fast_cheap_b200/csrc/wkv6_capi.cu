@@ -52,6 +52,10 @@ static encode_fn_t get_encode() {
 static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, int C, int rows) {
     encode_fn_t enc = get_encode();
     if (!enc) return fail(WKV6_E_NODRIVER, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    // cuTensorMapEncodeTiled wants a current context; threads that never touched the runtime (autograd workers)
+    // have none until a runtime call binds the primary context.
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) { cudaFree(nullptr); ctx_bound = true; }
     const size_t es = dtype == WKV6_DTYPE_BF16 ? 2 : 4;
     const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)T, (cuuint64_t)B};
     const cuuint64_t strides[2] = {(cuuint64_t)C * es, (cuuint64_t)T * C * es};
@@ -137,6 +141,8 @@ static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets
     return cuda_fail(e, "wkv6 forward launch");
 }
 
+extern "C" size_t wkv6_b200_backward_workspace_bytes(int, int, int, int, int, int);
+
 static int run_backward(int dtype, int B, int T, int C, int H, const BwdSet* sets, const int* reverse, int nset,
                         void* ws, size_t ws_bytes, void* stream) {
     int e = check_common(dtype, B, T, C, H);
@@ -176,11 +182,14 @@ static int run_backward(int dtype, int B, int T, int C, int H, const BwdSet* set
         d.gr = s.gr; d.gk = s.gk; d.gv = s.gv; d.gw = s.gw; d.gu = s.gu;
         d.reverse = reverse[i];
         d.hT = nullptr;
-        if (s.gsT) {
-            if (!ws || ws_bytes < per_dir * (size_t)nset || !aligned16(ws))
-                return fail(WKV6_E_WORKSPACE, "backward with gsT needs %zu workspace bytes (wkv6_b200_backward_workspace_bytes)",
-                            per_dir * (size_t)nset);
+        d.grlo = nullptr;
+        const size_t need = wkv6_b200_backward_workspace_bytes(dtype, B, T, C, H, nset);
+        if (s.gsT || dtype == WKV6_DTYPE_BF16) {
+            if (!ws || ws_bytes < need || !aligned16(ws))
+                return fail(WKV6_E_WORKSPACE, "backward needs %zu workspace bytes (wkv6_b200_backward_workspace_bytes)", need);
             d.hT = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + per_dir * i);
+            if (dtype == WKV6_DTYPE_BF16)
+                d.grlo = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(ws) + per_dir * nset + (size_t)B * T * C * 2 * i);
         }
     }
     e = launch_bwd_scan(dtype, p, (cudaStream_t)stream);
@@ -207,9 +216,10 @@ int wkv6_b200_forward(int dtype, int B, int T, int C, int H, const void* r, cons
 }
 
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
-    (void)dtype; (void)T; (void)C;
     if (B <= 0 || H <= 0 || ndirections <= 0) return 0;
-    return (size_t)ndirections * B * H * N * sizeof(float);
+    size_t n = (size_t)ndirections * B * H * N * sizeof(float);                    /* hT  */
+    if (dtype == WKV6_DTYPE_BF16 && T > 0) n += (size_t)ndirections * B * T * C * 2;  /* grlo */
+    return n;
 }
 
 int wkv6_b200_backward(int dtype, int B, int T, int C, int H, const void* r, const void* k, const void* v, const void* w,

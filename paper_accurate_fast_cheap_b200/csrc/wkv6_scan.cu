@@ -109,12 +109,14 @@ __device__ __forceinline__ void store_state(const float2 (&S)[4][4], float* s, c
 // =======================================================================================
 // forward
 // =======================================================================================
+constexpr int PSTR = 68;   // padded row of `part`: conflict-free 128-bit stores from 8 j-groups
+
 template <typename IO>
 struct FwdSmem {
     static constexpr int NS = io_traits<IO>::kStages;
     alignas(128) IO raw[NS][4][TT * N];   // TMA landing zone: r, k, v, w
     alignas(16) float f[2][4][TT * N];    // fp32: r, k, v, d = exp(-exp(w))
-    alignas(16) float out[2][TT * N];     // y tile
+    alignas(16) float part[TT * 8 * PSTR]; // per-step partial y of the 8 j-groups, rows padded to 68 floats
     float bonus[2][TT];                   // sum_j r u k per step
     alignas(8) uint64_t full[NS];
 };
@@ -189,57 +191,71 @@ __global__ void __launch_bounds__(NT, 2) wkv6_fwd_scan_kernel(const __grid_const
     };
 
     IO* const ybase = reinterpret_cast<IO*>(D.y) + (size_t)b * T * C + h * N + pc0;
-    const int asel = reduce4_index(tl.lane);
 
-    if (ntiles > 0) {
-        preprocess(0);
-        __syncthreads();
-        if (tid == 0 && NS < ntiles) issue(NS);
-    }
+    // Two barriers per 16-step tile.  Inside the step loop there is no cross-lane traffic at all: every thread
+    // parks its four partial sums (over its 8 j) in `part`, and the epilogue adds the 8 j-groups.  With one warp
+    // per scheduler per CTA, shuffle latency in the loop was the bound (215 us -> see profiles/).
+    auto step = [&](int buf, int s) {
+        const float* fr = sm.f[buf][0] + s * N;
+        const float* fk = sm.f[buf][1] + s * N;
+        const float* fv = sm.f[buf][2] + s * N;
+        const float* fd = sm.f[buf][3] + s * N;
+        float2 r2[4], k2[4], d2[4];
+        split4(*reinterpret_cast<const float4*>(fr + tl.jA), *reinterpret_cast<const float4*>(fr + tl.jB), r2);
+        split4(*reinterpret_cast<const float4*>(fk + tl.jA), *reinterpret_cast<const float4*>(fk + tl.jB), k2);
+        split4(*reinterpret_cast<const float4*>(fd + tl.jA), *reinterpret_cast<const float4*>(fd + tl.jB), d2);
+        const float4 v4 = *reinterpret_cast<const float4*>(fv + tl.i0);
+        const float va[4] = {v4.x, v4.y, v4.z, v4.w};
+        float ya[4];
+#pragma unroll
+        for (int a = 0; a < 4; a++) {
+            const float2 vv = make_float2(va[a], va[a]);
+            float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int qq = 0; qq < 4; qq++) {
+                acc = __ffma2_rn(r2[qq], S[a][qq], acc);
+                const float2 x = __fmul2_rn(k2[qq], vv);
+                S[a][qq] = __ffma2_rn(S[a][qq], d2[qq], x);
+            }
+            ya[a] = acc.x + acc.y;
+        }
+        *reinterpret_cast<float4*>(&sm.part[(s * 8 + tl.jg) * PSTR + tl.i0]) = make_float4(ya[0], ya[1], ya[2], ya[3]);
+    };
+
+    if (ntiles > 0) preprocess(0);
     for (int n = 0; n < ntiles; n++) {
         const int buf = n & 1;
         const int q = rev ? ntiles - 1 - n : n;
         const int nvalid = min(TT, T - q * TT);
-        if (n + 1 < ntiles) preprocess(n + 1);
-
-        for (int m = 0; m < nvalid; m++) {
-            const int s = rev ? nvalid - 1 - m : m;
-            const float* fr = sm.f[buf][0] + s * N;
-            const float* fk = sm.f[buf][1] + s * N;
-            const float* fv = sm.f[buf][2] + s * N;
-            const float* fd = sm.f[buf][3] + s * N;
-            float2 r2[4], k2[4], d2[4];
-            split4(*reinterpret_cast<const float4*>(fr + tl.jA), *reinterpret_cast<const float4*>(fr + tl.jB), r2);
-            split4(*reinterpret_cast<const float4*>(fk + tl.jA), *reinterpret_cast<const float4*>(fk + tl.jB), k2);
-            split4(*reinterpret_cast<const float4*>(fd + tl.jA), *reinterpret_cast<const float4*>(fd + tl.jB), d2);
-            const float4 v4 = *reinterpret_cast<const float4*>(fv + tl.i0);
-            const float va[4] = {v4.x, v4.y, v4.z, v4.w};
-            float ya[4];
-#pragma unroll
-            for (int a = 0; a < 4; a++) {
-                const float2 vv = make_float2(va[a], va[a]);
-                float2 acc = make_float2(0.f, 0.f);
-#pragma unroll
-                for (int qq = 0; qq < 4; qq++) {
-                    acc = __ffma2_rn(r2[qq], S[a][qq], acc);
-                    const float2 x = __fmul2_rn(k2[qq], vv);
-                    S[a][qq] = __ffma2_rn(S[a][qq], d2[qq], x);
-                }
-                ya[a] = acc.x + acc.y;
+        __syncthreads();   // f[buf] complete; previous epilogue done with `part`
+        if (tid == 0 && n + NS < ntiles) issue(n + NS);
+        if (nvalid == TT) {
+            if (rev) {
+#pragma unroll 4
+                for (int m = TT - 1; m >= 0; m--) step(buf, m);
+            } else {
+#pragma unroll 4
+                for (int m = 0; m < TT; m++) step(buf, m);
             }
-            const float yy = reduce4_over_j(ya, tl.lane);
-            if (!(tl.lane & 4)) {
-                const float vsel = (asel & 2) ? ((asel & 1) ? va[3] : va[2]) : ((asel & 1) ? va[1] : va[0]);
-                sm.out[buf][s * N + tl.i0 + asel] = fmaf(sm.bonus[buf][s], vsel, yy);
-            }
+        } else {
+            for (int m = 0; m < nvalid; m++) step(buf, rev ? nvalid - 1 - m : m);
         }
         __syncthreads();
-        if (tid == 0 && n + 1 + NS < ntiles) issue(n + 1 + NS);
         if (prow < nvalid) {
-            float o8[8];
-            ld8f(&sm.out[buf][prow * N + pc0], o8);
+            float o8[8], a8[8];
+            ld8f(&sm.f[buf][2][prow * N + pc0], o8);
+            const float bn = sm.bonus[buf][prow];
+#pragma unroll
+            for (int e = 0; e < 8; e++) o8[e] *= bn;
+#pragma unroll
+            for (int g = 0; g < 8; g++) {
+                ld8f(&sm.part[(prow * 8 + g) * PSTR + pc0], a8);
+#pragma unroll
+                for (int e = 0; e < 8; e++) o8[e] += a8[e];
+            }
             tr::store8(ybase + (size_t)(q * TT + prow) * C, o8);
         }
+        if (n + 1 < ntiles) preprocess(n + 1);
     }
     if (D.sT) store_state(S, D.sT + (size_t)bh * N * N, tl);
 }
@@ -387,6 +403,14 @@ __global__ void __launch_bounds__(NT, 2) wkv6_bwd_a_kernel(const __grid_constant
 #pragma unroll
             for (int e = 0; e < 8; e++) o8[e] = fmaf(u8[e] * k8[e], vg, o8[e]);
             tr::store8(grbase + (size_t)(q * TT + prow) * C, o8);
+            if constexpr (sizeof(IO) == 2) {
+                if (D.grlo) {   // low-order part of gr for sweep B (bf16 gr alone costs gw 2^-9 per summed term)
+                    float lo8[8];
+#pragma unroll
+                    for (int e = 0; e < 8; e++) lo8[e] = o8[e] - tr::to_float(tr::from_float(o8[e]));
+                    tr::store8(D.grlo + (size_t)b * T * C + h * N + pc0 + (size_t)(q * TT + prow) * C, lo8);
+                }
+            }
         }
         if (n + 1 < ntiles) preprocess(n + 1);
     }
@@ -497,6 +521,15 @@ __global__ void __launch_bounds__(NT, sizeof(IO) == 2 ? 2 : 1) wkv6_bwd_b_kernel
         tr::load8(&sm.raw[slot][3][prow * N + pc0], w8);
         tr::load8(&sm.raw[slot][4][prow * N + pc0], g8);
         tr::load8(&sm.raw[slot][5][prow * N + pc0], q8);
+        if constexpr (sizeof(IO) == 2) {
+            const int qq = brev ? ntiles - 1 - n : n;
+            if (D.grlo && qq * TT + prow < T) {
+                float lo8[8];
+                tr::load8(D.grlo + (size_t)b * T * C + h * N + pc0 + (size_t)(qq * TT + prow) * C, lo8);
+#pragma unroll
+                for (int e = 0; e < 8; e++) q8[e] += lo8[e];
+            }
+        }
         float vg = 0.f, bn = 0.f, ew8[8];
 #pragma unroll
         for (int e = 0; e < 8; e++) {
@@ -629,7 +662,11 @@ __global__ void __launch_bounds__(NT, sizeof(IO) == 2 ? 2 : 1) wkv6_bwd_b_kernel
                 if (m < nvalid) {
                     const int s = brev ? nvalid - 1 - m : m;
                     const float Hm = Xin - kg[mm];
-                    gwbase[(size_t)(q * TT + s) * C] = tr::from_float(-ew[mm] * Hm);
+                    // the direction's first step sees S_0: without an initial state gw is exactly 0 there
+                    // (the reference hard-codes it, wkv6_cuda.cu:237); the suffix sum only leaves rounding residue
+                    const int t = q * TT + s;
+                    const bool first = !D.s0 && (D.reverse ? t == T - 1 : t == 0);
+                    gwbase[(size_t)t * C] = tr::from_float(first ? 0.f : -ew[mm] * Hm);
                     Xin = Hm + av[mm];
                 }
             }

@@ -20,6 +20,8 @@ struct alignas(64) DirArgs {
     void *gr, *gk, *gv, *gw;              // [B,T,C]
     void* gu;                             // [B,C]
     float* hT;                            // workspace [B*H*64]: sum_i S_T[i][j]*gsT[i][j]  (pass A -> pass B)
+    __nv_bfloat16* grlo;                  // workspace [B,T,C] (bf16 I/O only): gr_fp32 - float(bf16(gr)), so that
+                                          // sweep B sees gr to ~16 mantissa bits for the gw suffix sum
     int reverse;                          // scan t = T-1..0
     int pad_;
 };

@@ -75,7 +75,7 @@ def wkv6_backward_raw(r, k, v, w, u, gy, s0=None, gsT=None, reverse=False, want_
     gu = torch.empty((B, C), device=r.device, dtype=r.dtype)
     gs0 = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_gs0 else None
     L = _lib.lib()
-    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, 1) if gsT is not None else 0
+    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, 1)
     ws = torch.empty(ws_bytes, device=r.device, dtype=torch.uint8) if ws_bytes else None
     with torch.cuda.device(r.device):
         _lib.check(L.wkv6_b200_backward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u), _p(s0),
@@ -129,8 +129,7 @@ def bi_backward_raw(f, b, gy_f, gy_b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None
 
     of, ob = outs(run_f), outs(run_b)
     L = _lib.lib()
-    need_ws = (gsT_f is not None) or (gsT_b is not None)
-    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(ref[0]), B, T, C, H, 2) if need_ws else 0
+    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(ref[0]), B, T, C, H, 2)
     ws = torch.empty(ws_bytes, device=dev, dtype=torch.uint8) if ws_bytes else None
     none5 = (None,) * 5
     fa = tuple(_p(t) for t in f) if run_f else none5

@@ -38,7 +38,8 @@ def test_argument_validation_without_gpu(built):
     # empty batch is a no-op; NULL tensors with work to do are rejected before any launch
     assert L.wkv6_b200_forward(0, 0, 4, 64, 1, None, None, None, None, None, None, None, None, 0, None) == 0
     assert L.wkv6_b200_forward(0, 1, 4, 64, 1, None, None, None, None, None, None, None, None, 0, None) == -1
-    assert L.wkv6_b200_backward_workspace_bytes(0, 2, 10, 128, 2, 2) == 2 * 2 * 2 * 64 * 4
+    assert L.wkv6_b200_backward_workspace_bytes(1, 2, 10, 128, 2, 2) == 2 * 2 * 2 * 64 * 4
+    assert L.wkv6_b200_backward_workspace_bytes(0, 2, 10, 128, 2, 2) == 2 * 2 * 2 * 64 * 4 + 2 * 2 * 10 * 128 * 2
 
 
 def test_torch_shim_registers_reference_schemas(built):
