@@ -49,7 +49,7 @@ static encode_fn_t get_encode() {
 }
 
 // 3-D view [B][T][C] of a contiguous tensor, box = [1][rows][64 channels]
-static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, int C, int rows) {
+static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, int C, int rows, bool swizzle128 = false) {
     encode_fn_t enc = get_encode();
     if (!enc) return fail(WKV6_E_NODRIVER, "cuTensorMapEncodeTiled is not available from the CUDA driver");
     // cuTensorMapEncodeTiled wants a current context; threads that never touched the runtime (autograd workers)
@@ -63,7 +63,8 @@ static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, in
     const cuuint32_t estr[3] = {1u, 1u, 1u};
     const CUresult r = enc(m, dtype == WKV6_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
                            3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(WKV6_E_BADARG, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return 0;
@@ -107,11 +108,11 @@ static int fill_fwd(DirArgs& d, int dtype, int B, int T, int C, const FwdSet& s,
     if (!s.u) return fail(WKV6_E_BADARG, "forward: u is NULL");
     if ((s.s0 && !aligned16(s.s0)) || (s.sT && !aligned16(s.sT))) return fail(WKV6_E_BADARG, "forward: misaligned state");
     int e;
-    if ((e = make_map(&d.mr, dtype, s.r, B, T, C, rows))) return e;
-    if ((e = make_map(&d.mk, dtype, s.k, B, T, C, rows))) return e;
-    if ((e = make_map(&d.mv, dtype, s.v, B, T, C, rows))) return e;
-    if ((e = make_map(&d.mw, dtype, s.w, B, T, C, rows))) return e;
-    if (want_ymap && (e = make_map(&d.my, dtype, s.y, B, T, C, rows))) return e;
+    if ((e = make_map(&d.mr, dtype, s.r, B, T, C, rows, want_ymap))) return e;
+    if ((e = make_map(&d.mk, dtype, s.k, B, T, C, rows, want_ymap))) return e;
+    if ((e = make_map(&d.mv, dtype, s.v, B, T, C, rows, want_ymap))) return e;
+    if ((e = make_map(&d.mw, dtype, s.w, B, T, C, rows, want_ymap))) return e;
+    if (want_ymap && (e = make_map(&d.my, dtype, s.y, B, T, C, rows, true))) return e;
     d.u = s.u; d.s0 = s.s0; d.sT = s.sT; d.y = s.y;
     d.reverse = reverse;
     return 0;
