@@ -51,7 +51,7 @@ def test_forward_matches_oracle(dtype, rev, B, T, H, with_state, w_mode):
     tol = TOL[dtype]
     assert y.dtype == dtype and sT.dtype == torch.float32
     assert oracle.rel_err(y, y_ref) <= tol
-    assert oracle.rel_err(sT, sT_ref) <= (1e-5 if dtype == torch.float32 else 1e-5)   # state is fp32 in both
+    assert oracle.rel_err(sT, sT_ref) <= tol   # bf16: the chunk kernel feeds bf16 operands to the tensor cores
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
@@ -109,7 +109,10 @@ def test_bidirectional_one_launch_and_direction_flags(dtype):
     # flip-free reversed direction == flip -> scan -> flip
     fl = lambda t: torch.flip(t, [1]).contiguous()
     y_flip, _ = pk.wkv6_forward_raw(fl(gb["r"]), fl(gb["k"]), fl(gb["v"]), fl(gb["w"]), gb["u"])
-    assert torch.equal(fl(y_flip), y_b)
+    if dtype == torch.float32:
+        assert torch.equal(fl(y_flip), y_b)          # exact scan: bit-identical
+    else:
+        assert oracle.rel_err(fl(y_flip), y_b) <= 2e-2  # chunk kernel: chunk boundaries differ after a flip
     # direction dropout flags
     y_f2, y_b2, _, _ = pk.bi_forward_raw(f, r_, flags=_lib.BI_L2R)
     assert y_b2 is None and torch.equal(y_f2, y_f)
