@@ -188,3 +188,27 @@ def test_rejects_bad_arguments():
     c = torch.zeros(1, 4, 64)
     with pytest.raises(AssertionError):
         pk.wkv6_forward_raw(c, c, c, c, torch.zeros(1, 64))   # CPU tensors: no fallback
+
+
+def _golden_cases():
+    import glob
+    import os
+    return sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "refcuda_*.npz")))
+
+
+@pytest.mark.parametrize("path", _golden_cases(), ids=[p.split("refcuda_")[-1][:-4] for p in _golden_cases()])
+def test_matches_reference_cuda_golden_vectors(path):
+    """CUDA path vs the committed outputs of the reference's own CUDA kernels (tests/golden/refcuda_*.npz).
+    Both sides carry their own rounding: the bound is the sum of the two errors vs fp64 truth."""
+    from test_golden import load_case
+    pk = _pkg()
+    c = load_case(path)
+    g = _cuda(c["inp"])
+    bf = c["dtype"] == "torch.bfloat16"
+    tol = 2e-2 if bf else 1e-5
+    y, _ = pk.wkv6_forward_raw(g["r"], g["k"], g["v"], g["w"], g["u"])
+    assert oracle.rel_err(y[:, ::c["stride"]], c["outs"]["y"]) <= tol
+    if c["bwd"]:
+        got = pk.wkv6_backward_raw(g["r"], g["k"], g["v"], g["w"], g["u"], g["gy"])
+        for name, a in zip(("gr", "gk", "gv", "gw", "gu"), got[:5]):
+            assert oracle.rel_err(a, c["outs"][name]) <= tol, name
