@@ -101,8 +101,9 @@ int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
                           int flags, void* workspace, size_t workspace_bytes, void* stream);
 
 /* out[i] = (a[i] + b[i]) * scale as fp32, a/b in `dtype`; b may be NULL (out = a*scale).
- * n = number of elements. */
-int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float scale,
+ * n = number of elements.  round_sum != 0 (bf16 only): the sum is rounded to bf16 (RNE) before the
+ * scale, bit-identical to the reference's `(x_f + x_b) / 2` in bf16 followed by `.float()`. */
+int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum,
                       float* out, void* stream);
 
 #ifdef __cplusplus

@@ -51,7 +51,7 @@ def lib() -> ctypes.CDLL:
     L.wkv6_b200_bi_forward.restype = _i
     L.wkv6_b200_bi_backward.argtypes = [_i] * 5 + [_vp] * 28 + [_i, _vp, _sz, _vp]
     L.wkv6_b200_bi_backward.restype = _i
-    L.wkv6_b200_combine.argtypes = [_i, _sz, _vp, _vp, ctypes.c_float, _vp, _vp]
+    L.wkv6_b200_combine.argtypes = [_i, _sz, _vp, _vp, ctypes.c_float, _i, _vp, _vp]
     L.wkv6_b200_combine.restype = _i
     _lib = L
     return L

@@ -156,3 +156,24 @@ def bi_wkv6(fwd_set, bwd_set, run_l2r: bool = True, run_r2l: bool = True):
     assert flags, "bi_wkv6: at least one direction must run"
     y_f, y_b = BiWKV6.apply(flags, *fwd_set, *bwd_set)
     return (y_f if run_l2r else None), (y_b if run_r2l else None)
+
+
+class Combine(torch.autograd.Function):
+    """out = (a + b) * scale as float32 in one fused pass (rwkv_wrapper_bidirectional.py:48-56).
+    `round_sum` rounds a + b to bf16 first, like the reference's bf16 add."""
+
+    @staticmethod
+    def forward(ctx, a, b, scale, round_sum):
+        ctx.scale, ctx.dt = float(scale), a.dtype
+        with torch.no_grad():
+            return ops.combine(a.contiguous(), b.contiguous(), ctx.scale, round_sum)
+
+    @staticmethod
+    def backward(ctx, g):
+        ga = (g * ctx.scale).to(ctx.dt)
+        return ga, ga, None, None
+
+
+def combine(a, b, scale: float = 0.5, round_sum: bool = False, out_float: bool = True):
+    out = Combine.apply(a, b, scale, bool(round_sum) and a.dtype == torch.bfloat16)
+    return out if out_float else out.to(a.dtype)

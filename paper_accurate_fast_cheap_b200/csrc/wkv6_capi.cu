@@ -261,12 +261,13 @@ int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
     return run_backward(dtype, B, T, C, H, sets, rv, n, workspace, workspace_bytes, stream);
 }
 
-int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float scale, float* out, void* stream) {
+int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out,
+                      void* stream) {
     if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
     if (n == 0) return 0;
     if (!a || !out || !aligned16(a) || !aligned16(out) || (b && !aligned16(b)) || (n % 8))
         return fail(WKV6_E_BADARG, "combine: NULL/misaligned pointer or n %% 8 != 0");
-    return cuda_fail(launch_combine(dtype, n, a, b, scale, out, (cudaStream_t)stream), "wkv6 combine launch");
+    return cuda_fail(launch_combine(dtype, n, a, b, scale, round_sum, out, (cudaStream_t)stream), "wkv6 combine launch");
 }
 
 }  // extern "C"

@@ -682,7 +682,7 @@ __global__ void __launch_bounds__(NT, sizeof(IO) == 2 ? 2 : 1) wkv6_bwd_b_kernel
 // =======================================================================================
 template <typename IO>
 __global__ void __launch_bounds__(256) wkv6_combine_kernel(size_t n8, const IO* __restrict__ a, const IO* __restrict__ b,
-                                                           float scale, float* __restrict__ out) {
+                                                           float scale, int round_sum, float* __restrict__ out) {
     using tr = io_traits<IO>;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
         float x[8], y[8];
@@ -691,6 +691,10 @@ __global__ void __launch_bounds__(256) wkv6_combine_kernel(size_t n8, const IO* 
             tr::load8(b + i * 8, y);
 #pragma unroll
             for (int e = 0; e < 8; e++) x[e] += y[e];
+            if (round_sum) {
+#pragma unroll
+                for (int e = 0; e < 8; e++) x[e] = tr::to_float(tr::from_float(x[e]));
+            }
         }
 #pragma unroll
         for (int e = 0; e < 8; e++) x[e] *= scale;
@@ -740,14 +744,14 @@ int launch_bwd_scan(int dtype, const Params& p, cudaStream_t st) {
     return dtype == 0 ? launch_bwd_t<__nv_bfloat16>(p, st) : launch_bwd_t<float>(p, st);
 }
 
-int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, float* out, cudaStream_t st) {
+int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out, cudaStream_t st) {
     const size_t n8 = n / 8;
     if (n8 == 0) return 0;
     const int blocks = (int)((n8 + 255) / 256 < 148 * 8 ? (n8 + 255) / 256 : 148 * 8);
     if (dtype == 0)
-        wkv6_combine_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(n8, (const __nv_bfloat16*)a, (const __nv_bfloat16*)b, scale, out);
+        wkv6_combine_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(n8, (const __nv_bfloat16*)a, (const __nv_bfloat16*)b, scale, round_sum, out);
     else
-        wkv6_combine_kernel<float><<<blocks, 256, 0, st>>>(n8, (const float*)a, (const float*)b, scale, out);
+        wkv6_combine_kernel<float><<<blocks, 256, 0, st>>>(n8, (const float*)a, (const float*)b, scale, 0, out);
     count_launch(1);
     return (int)cudaGetLastError();
 }

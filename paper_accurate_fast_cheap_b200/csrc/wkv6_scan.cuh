@@ -36,7 +36,7 @@ struct Params {
 int launch_fwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_bwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_fwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05
-int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, float* out, cudaStream_t st);
+int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out, cudaStream_t st);
 
 void count_launch(int n);
 

@@ -143,10 +143,11 @@ def bi_backward_raw(f, b, gy_f, gy_b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None
     return of, ob
 
 
-def combine(a: torch.Tensor, b: Optional[torch.Tensor], scale: float = 0.5) -> torch.Tensor:
+def combine(a: torch.Tensor, b: Optional[torch.Tensor], scale: float = 0.5, round_sum: bool = False) -> torch.Tensor:
     """(a + b) * scale as float32 in one pass (rwkv_wrapper_bidirectional.py:48-56)."""
     assert a.is_cuda and a.is_contiguous() and (b is None or (b.is_contiguous() and b.shape == a.shape and b.dtype == a.dtype))
     out = torch.empty(a.shape, device=a.device, dtype=torch.float32)
     with torch.cuda.device(a.device):
-        _lib.check(_lib.lib().wkv6_b200_combine(_dtype_code(a), a.numel(), _p(a), _p(b), float(scale), _p(out), _stream(a)))
+        _lib.check(_lib.lib().wkv6_b200_combine(_dtype_code(a), a.numel(), _p(a), _p(b), float(scale), int(bool(round_sum)),
+                                                _p(out), _stream(a)))
     return out

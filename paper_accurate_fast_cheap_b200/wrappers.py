@@ -1,0 +1,264 @@
+"""Host-side mirror of the reference's attention-slot modules for the WKV6 path.
+
+Same class names, constructor signatures, parameter / state-dict names, forward signatures and return values as
+
+    wenet/rwkv_v6/src/model.py:217-325                                   RWKV_Tmix_x060c
+    wenet/rwkv_v6/rwkv_wrapper.py:5-83                                   RWKV_TmixWrapper
+    wenet/rwkv_v6/rwkv_wrapper_bidirectional.py:7-64                     RWKV_TmixWrapper_bidirectional
+    wenet/rwkv_v6/rwkv_wrapper_bidirectional_direction_dropout.py:7-97   ..._direction_dropout
+    wenet/rwkv_v6/rwkv_wrapper_bidirectional_direction_dropout_both.py   ..._direction_dropout_both
+
+so a checkpoint of the reference loads unchanged and `install()` can swap them into wenet's
+`WENET_ATTENTION_CLASSES` (wenet/utils/class_utils.py:82-86).  What is different is HOW the block runs:
+
+* the right-to-left direction never flips anything: its token shift is `x[t+1] - x[t]`, every
+  other prologue/epilogue op is position-wise, and the scan itself walks t = T-1..0 inside the kernel;
+* both directions' scans are ONE launch (`bi_wkv6`), direction dropout becomes the launch's `flags`;
+* `(fwd + bwd) / 2` (+ the cast to float) is one fused pass (`combine`).
+
+The GEMMs / LayerNorm around the scan stay torch ops ("surrounds the op, runs unchanged").
+No CPU path: the scan raises on CPU tensors.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _lib, autograd, ops
+
+
+class RWKV_Tmix_x060c(nn.Module):
+    """Parameters, initialisation order (RNG-identical) and math of model.py:217-325."""
+
+    def __init__(self, head_size: int, n_layers: int, n_embd: int, dim_att: int, layer_id: int):
+        super().__init__()
+        self.layer_id, self.head_size, self.n_head = layer_id, head_size, dim_att // head_size
+        self.dim_att, self.n_embd, self.n_layers = dim_att, n_embd, n_layers
+        assert dim_att % self.n_head == 0
+        with torch.no_grad():
+            ratio_0_to_1 = layer_id / (n_layers - 1)
+            ratio_1_to_almost0 = 1.0 - (layer_id / n_layers)
+            ddd = (torch.arange(n_embd, dtype=torch.float64) / n_embd).float().view(1, 1, n_embd)
+            self.time_maa_x = nn.Parameter(1.0 - torch.pow(ddd, ratio_1_to_almost0))
+            self.time_maa_r = nn.Parameter(1.0 - torch.pow(ddd, 0.5 * ratio_1_to_almost0))
+            self.time_maa_k = nn.Parameter(1.0 - torch.pow(ddd, ratio_1_to_almost0))
+            self.time_maa_v = nn.Parameter(1.0 - (torch.pow(ddd, ratio_1_to_almost0) + 0.3 * ratio_0_to_1))
+            self.time_maa_w = nn.Parameter(1.0 - torch.pow(ddd, ratio_1_to_almost0))
+            self.time_maa_rkvw_w1 = nn.Parameter(torch.zeros(n_embd, 32 * 4))
+            self.time_maa_rkvw_w2 = nn.Parameter(torch.zeros(4, 32, n_embd).uniform_(-0.01, 0.01))
+            n = torch.arange(dim_att, dtype=torch.float64)
+            decay_speed = (-6 + 5 * (n / (dim_att - 1)) ** (0.7 + 1.3 * ratio_0_to_1)).float()
+            self.time_decay = nn.Parameter(decay_speed.reshape(1, 1, dim_att))
+            self.time_decay_w1 = nn.Parameter(torch.zeros(n_embd, 64))
+            self.time_decay_w2 = nn.Parameter(torch.zeros(64, dim_att).uniform_(-0.01, 0.01))
+            zigzag = ((n + 1) % 3 - 1) * 0.1
+            faaaa = (ratio_0_to_1 * (1 - (n / (dim_att - 1))) + zigzag).float()
+            self.time_faaaa = nn.Parameter(faaaa.reshape(self.n_head, head_size))
+        self.receptance = nn.Linear(n_embd, dim_att, bias=False)
+        self.key = nn.Linear(n_embd, dim_att, bias=False)
+        self.value = nn.Linear(n_embd, dim_att, bias=False)
+        self.output = nn.Linear(dim_att, n_embd, bias=False)
+        self.ln_x = nn.LayerNorm(dim_att)
+
+    def prologue(self, x: torch.Tensor, reverse: bool = False):
+        """x [B,T,C] -> contiguous r, k, v, w (model.py:270-289).  `reverse`: the token shift looks at t+1."""
+        B, T, C = x.size()
+        if reverse:
+            xx = F.pad(x[:, 1:], (0, 0, 0, 1)) - x
+        else:
+            xx = F.pad(x[:, :-1], (0, 0, 1, 0)) - x                      # nn.ZeroPad2d((0,0,1,-1))
+        xxx = x + xx * self.time_maa_x
+        xxx = torch.tanh(xxx @ self.time_maa_rkvw_w1).view(B * T, 4, -1).transpose(0, 1)
+        xxx = torch.bmm(xxx, self.time_maa_rkvw_w2).view(4, B, T, C)
+        mr, mk, mv, mw = xxx.unbind(dim=0)
+        r = self.receptance(x + xx * (self.time_maa_r + mr))
+        k = self.key(x + xx * (self.time_maa_k + mk))
+        v = self.value(x + xx * (self.time_maa_v + mv))
+        ww = x + xx * (self.time_maa_w + mw)
+        w = self.time_decay + torch.tanh(ww @ self.time_decay_w1) @ self.time_decay_w2
+        return r.contiguous(), k.contiguous(), v.contiguous(), w.contiguous()
+
+    def epilogue(self, y: torch.Tensor) -> torch.Tensor:
+        return self.output(self.ln_x(y))                                  # model.py:323-324
+
+    def forward(self, x: torch.Tensor, reverse: bool = False) -> torch.Tensor:
+        r, k, v, w = self.prologue(x, reverse)
+        if reverse:
+            y, _ = autograd.wkv6(r, k, v, w, self.time_faaaa, None, True)
+        elif x.dtype == torch.float32:
+            y = autograd.RUN_CUDA_RWKV6_FP32(r, k, v, w, self.time_faaaa)     # model.py:296-299
+        else:
+            y = autograd.RUN_CUDA_RWKV6(r, k, v, w, self.time_faaaa)
+        return self.epilogue(y)
+
+
+_EMPTY_MASK = torch.ones((0, 0, 0), dtype=torch.bool)
+_EMPTY_POS = torch.empty(0)
+_EMPTY_CACHE = torch.zeros((0, 0, 0, 0))
+
+
+class RWKV_TmixWrapper(nn.Module):
+    """Unidirectional attention-slot wrapper (rwkv_wrapper.py:5-83): MHA-shaped signature, cache passed through."""
+
+    def __init__(self, head_size: int, dim_att: int, num_blocks: int, rnn_att_version: Optional[str] = None,
+                 rnn_att_direction: Optional[str] = None, ctx_len: int = 2048, do_bfloat16: bool = True,
+                 layer_id: int = 1):
+        super().__init__()
+        self.head_size, self.dim_att, self.num_blocks = head_size, dim_att, num_blocks
+        self.rnn_att_version, self.rnn_att_direction = rnn_att_version, rnn_att_direction
+        self.ctx_len, self.do_bfloat16, self.layer_id = ctx_len, do_bfloat16, layer_id      # ctx_len: no T limit here
+        self.n_head, self.n_embd = dim_att // head_size, dim_att
+        assert head_size == ops.HEAD_SIZE, "this build supports head_size 64 (every shipped config)"
+        self.tmix_block = RWKV_Tmix_x060c(head_size=head_size, n_layers=num_blocks, n_embd=dim_att, dim_att=dim_att,
+                                          layer_id=layer_id)
+        if do_bfloat16:
+            self.tmix_block = self.tmix_block.to(dtype=torch.bfloat16)
+
+    def forward(self, query, key=None, value=None, mask=_EMPTY_MASK, pos_emb=_EMPTY_POS, cache=_EMPTY_CACHE
+                ) -> Tuple[torch.Tensor, torch.Tensor]:
+        qd = query.dtype
+        x = query.to(dtype=torch.bfloat16) if self.do_bfloat16 else query
+        out = self.tmix_block(x)
+        if self.do_bfloat16:
+            out = out.to(dtype=qd)
+        return out, cache
+
+
+def _bi_block(fwd: RWKV_Tmix_x060c, bwd: RWKV_Tmix_x060c, x: torch.Tensor, run_l2r: bool, run_r2l: bool):
+    """Both Tmix blocks on the same un-flipped x: prologues, ONE scan launch, epilogues.  Returns (out_f, out_b) in
+    x's dtype at natural time positions; None for a direction that did not run."""
+    set_f = (*fwd.prologue(x, reverse=False), fwd.time_faaaa) if run_l2r else None
+    set_b = (*bwd.prologue(x, reverse=True), bwd.time_faaaa) if run_r2l else None
+    y_f, y_b = autograd.bi_wkv6(set_f if run_l2r else set_b, set_b if run_r2l else set_f, run_l2r, run_r2l)
+    return (fwd.epilogue(y_f) if run_l2r else None), (bwd.epilogue(y_b) if run_r2l else None)
+
+
+class _BiBase(nn.Module):
+    def _make(self, head_size, dim_att, num_blocks, ver, direction, ctx_len, do_bfloat16, layer_id):
+        self.rwkv_wrapper_forward = RWKV_TmixWrapper(head_size, dim_att, num_blocks, ver, direction, ctx_len,
+                                                     do_bfloat16, layer_id)
+        self.rwkv_wrapper_backward = RWKV_TmixWrapper(head_size, dim_att, num_blocks, ver, direction, ctx_len,
+                                                      do_bfloat16, layer_id)
+
+    def _blocks(self):
+        return self.rwkv_wrapper_forward.tmix_block, self.rwkv_wrapper_backward.tmix_block
+
+
+class RWKV_TmixWrapper_bidirectional(_BiBase):
+    """out = (F(x) + flip(G(flip(x)))) / 2, .float()  (rwkv_wrapper_bidirectional.py:30-64), flip-free."""
+
+    def __init__(self, head_size: int, dim_att: int, num_blocks: int, rnn_att_version: str = None,
+                 rnn_att_direction: str = None, ctx_len: int = 2048, do_bfloat16: bool = True, layer_id: int = 1):
+        super().__init__()
+        self.do_bfloat16 = do_bfloat16
+        self._make(head_size, dim_att, num_blocks, rnn_att_version, rnn_att_direction, ctx_len, do_bfloat16, layer_id)
+        self.rwkv_wrapper_forward.do_bfloat16 = False          # conversion handled here, as in the reference (:25-28)
+        self.rwkv_wrapper_backward.do_bfloat16 = False
+
+    def forward(self, query, key=None, value=None, mask=_EMPTY_MASK, pos_emb=_EMPTY_POS, cache=_EMPTY_CACHE):
+        x = query.to(dtype=torch.bfloat16) if self.do_bfloat16 else query
+        o_f, o_b = _bi_block(*self._blocks(), x, True, True)
+        # the reference adds and halves in x's dtype, then casts (:48-54): round_sum reproduces the bf16 rounding
+        out = autograd.combine(o_f, o_b, 0.5, round_sum=self.do_bfloat16, out_float=True)
+        if not self.do_bfloat16:
+            out = out.to(query.dtype)
+        return out, cache
+
+    forward_parallel = forward                                  # :66-116: same result, two streams in the reference
+
+
+class RWKV_TmixWrapper_bidirectional_direction_dropout(_BiBase):
+    """Training: L2R always, R2L kept with p = 0.8 (one CPU Bernoulli draw per call, ..._dropout.py:59-69).
+    Eval: bidirectional / alternating / L2R-only by RWKV_BIDIRECTIONAL_LAYERS and RWKV_ALT_DECODING (:22-33,70-91)."""
+    BOTH = False
+
+    def __init__(self, head_size: int, dim_att: int, num_blocks: int, rnn_att_version: str = None,
+                 rnn_att_direction: str = None, ctx_len: int = 2048, do_bfloat16: bool = True, layer_id: int = 1):
+        super().__init__()
+        self.layer_id = layer_id
+        self.do_bfloat16 = do_bfloat16
+        self.bi_layers_actives = []
+        self.bi_active = True
+        self.alt_decoding = os.environ.get("RWKV_ALT_DECODING", "0") == "1"
+        if os.environ.get("RWKV_BIDIRECTIONAL_LAYERS"):
+            self.bi_layers_actives = [int(v) for v in os.environ.get("RWKV_BIDIRECTIONAL_LAYERS").split(",")]
+            if layer_id not in self.bi_layers_actives:
+                self.bi_active = False
+        self._make(head_size, dim_att, num_blocks, rnn_att_version, rnn_att_direction, ctx_len, do_bfloat16, layer_id)
+
+    def _directions(self) -> Tuple[bool, bool]:
+        if self.training:
+            p = 0.2
+            keep = torch.distributions.bernoulli.Bernoulli(1 - p).sample((1,))
+            if keep == 1:
+                return True, True
+            if not self.BOTH:
+                return True, False
+            choose = torch.distributions.bernoulli.Bernoulli(1 - p).sample((1,))     # ..._both.py:63-71
+            return (True, False) if choose <= 0.5 else (False, True)
+        if self.bi_active:
+            return True, True
+        if self.alt_decoding:
+            return (True, False) if self.layer_id % 2 == 0 else (False, True)
+        return True, False
+
+    def forward(self, query, key=None, value=None, mask=_EMPTY_MASK, pos_emb=_EMPTY_POS, cache=_EMPTY_CACHE):
+        run_f, run_b = self._directions()
+        qd = query.dtype
+        x = query.to(dtype=torch.bfloat16) if self.do_bfloat16 else query      # inner wrappers cast per direction
+        o_f, o_b = _bi_block(*self._blocks(), x, run_f, run_b)
+        if run_f and run_b:
+            # inner wrappers hand back query-dtype tensors; the reference averages those (fp32 when the encoder is)
+            out = autograd.combine(o_f, o_b, 0.5, round_sum=False, out_float=(qd == torch.float32)).to(qd)
+        else:
+            out = (o_f if run_f else o_b).to(qd)
+        return out, cache
+
+
+class RWKV_TmixWrapper_bidirectional_direction_dropout_both(RWKV_TmixWrapper_bidirectional_direction_dropout):
+    """As above, but a dropped step keeps L2R w.p. 0.2 and R2L w.p. 0.8 (the `choose <= 0.5` quirk)."""
+    BOTH = True
+
+
+# the five keys of WENET_ATTENTION_CLASSES this path owns (wenet/utils/class_utils.py:82-86)
+WENET_ATTENTION_CLASSES_B200 = {
+    "rwkv_tmix60": RWKV_TmixWrapper,
+    "rwkv_tmix60_bidirectional": RWKV_TmixWrapper_bidirectional,
+    "rwkv_tmix60_bidirectional2": RWKV_TmixWrapper_bidirectional,
+    "rwkv_tmix60_dir_layer_drop": RWKV_TmixWrapper_bidirectional_direction_dropout,
+    "rwkv_tmix60_dir_layer_drop_both": RWKV_TmixWrapper_bidirectional_direction_dropout_both,
+}
+
+
+def install_ops() -> None:
+    """Makes the UNMODIFIED reference model.py use these kernels: registers torch.ops.wkv6.* (same schemas as
+    wkv6_op.cpp:9-41) and turns the reference's JIT build of its own `wkv6` extension (model.py:105-106) into a
+    no-op -- a second TORCH_LIBRARY(wkv6) would abort.  Call before importing wenet.rwkv_v6.src.model."""
+    _lib.load_torch_ops()
+    from torch.utils import cpp_extension
+    if getattr(cpp_extension.load, "_wkv6_b200", False):
+        return
+    orig = cpp_extension.load
+
+    def load(name, *a, **kw):
+        if name == "wkv6":
+            return None
+        return orig(name, *a, **kw)
+
+    load._wkv6_b200 = True
+    cpp_extension.load = load
+
+
+def install(class_utils=None) -> None:
+    """install_ops() + swap the five attention classes in wenet.utils.class_utils (if given or importable)."""
+    install_ops()
+    if class_utils is None:
+        try:
+            from wenet.utils import class_utils as class_utils     # noqa: PLC0415
+        except Exception:
+            return
+    class_utils.WENET_ATTENTION_CLASSES.update(WENET_ATTENTION_CLASSES_B200)
