@@ -175,11 +175,15 @@ def run_b200(args):
     flags = _lib.BI_L2R | _lib.BI_R2L
     p = lambda t: t.data_ptr()
 
+    ck_bytes = L.wkv6_b200_checkpoint_bytes(B, T, C, H) if train else 0
+    ckpts = [torch.empty((2, ck_bytes), device=dev, dtype=torch.uint8) for _ in range(NL)] if train else None
+    ck = lambda l, d: (ckpts[l][d].data_ptr() if train else None)
+
     def fwd_layer(l, ins=None, ys=None):
         f, b = ins or layers[l]
         yf, yb = ys or outs[l]
-        _lib.check(L.wkv6_b200_bi_forward(0, B, T, C, H, p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(yf), None,
-                                          p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(yb), None, flags, stream))
+        _lib.check(L.wkv6_b200_bi_forward(0, B, T, C, H, p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(yf), None, ck(l, 0),
+                                          p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(yb), None, ck(l, 1), flags, stream))
 
     ws_bytes = L.wkv6_b200_backward_workspace_bytes(0, B, T, C, H, 2) if train else 0
     ws = torch.empty(max(ws_bytes, 16), device=dev, dtype=torch.uint8)
@@ -189,8 +193,8 @@ def run_b200(args):
         gf, gb = gouts[l]
         _lib.check(L.wkv6_b200_bi_backward(
             0, B, T, C, H,
-            p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(f[5]), None, *[p(x) for x in gf], None,
-            p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(b[5]), None, *[p(x) for x in gb], None,
+            p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(f[5]), None, ck(l, 0), *[p(x) for x in gf], None,
+            p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(b[5]), None, ck(l, 1), *[p(x) for x in gb], None,
             flags, p(ws), ws_bytes, stream))
 
     ev_pairs = []

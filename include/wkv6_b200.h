@@ -68,16 +68,22 @@ long long wkv6_b200_launch_count(void);
 void wkv6_b200_set_algo(int algo);
 int  wkv6_b200_get_algo(void);
 
+/* Bytes of one direction's checkpoint buffer (bf16 state at the start of every 64-step chunk):
+ * B*H*ceil(T/64)*64*64*2.  A forward that is given `ckpt` (bf16 I/O, tcgen05 chunk kernel) fills it; a backward
+ * that is given the same buffer skips the state recomputation.  The reference keeps nothing between its forward
+ * and backward launches (model.py:131,149), so NULL is always accepted. */
+size_t wkv6_b200_checkpoint_bytes(int B, int T, int C, int H);
+
 int wkv6_b200_forward(int dtype, int B, int T, int C, int H,
                       const void* r, const void* k, const void* v, const void* w, const void* u,
-                      const float* s0, void* y, float* sT, int reverse, void* stream);
+                      const float* s0, void* y, float* sT, void* ckpt, int reverse, void* stream);
 
 /* Bytes of scratch the backward entry points need (0 is possible). */
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections);
 
 int wkv6_b200_backward(int dtype, int B, int T, int C, int H,
                        const void* r, const void* k, const void* v, const void* w, const void* u,
-                       const float* s0, const void* gy, const float* gsT,
+                       const float* s0, const void* gy, const float* gsT, const void* ckpt,
                        void* gr, void* gk, void* gv, void* gw, void* gu, float* gs0,
                        int reverse, void* workspace, size_t workspace_bytes, void* stream);
 
@@ -86,17 +92,17 @@ int wkv6_b200_backward(int dtype, int B, int T, int C, int H,
  * bit is clear is neither read nor written. */
 int wkv6_b200_bi_forward(int dtype, int B, int T, int C, int H,
                          const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
-                         const float* s0_f, void* y_f, float* sT_f,
+                         const float* s0_f, void* y_f, float* sT_f, void* ckpt_f,
                          const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
-                         const float* s0_b, void* y_b, float* sT_b,
+                         const float* s0_b, void* y_b, float* sT_b, void* ckpt_b,
                          int flags, void* stream);
 
 int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
                           const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
-                          const float* s0_f, const void* gy_f, const float* gsT_f,
+                          const float* s0_f, const void* gy_f, const float* gsT_f, const void* ckpt_f,
                           void* gr_f, void* gk_f, void* gv_f, void* gw_f, void* gu_f, float* gs0_f,
                           const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
-                          const float* s0_b, const void* gy_b, const float* gsT_b,
+                          const float* s0_b, const void* gy_b, const float* gsT_b, const void* ckpt_b,
                           void* gr_b, void* gk_b, void* gv_b, void* gw_b, void* gu_b, float* gs0_b,
                           int flags, void* workspace, size_t workspace_bytes, void* stream);
 

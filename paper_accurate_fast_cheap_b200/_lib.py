@@ -15,7 +15,7 @@ ALGO_AUTO, ALGO_SCAN, ALGO_CHUNK = 0, 1, 2
 # every symbol include/wkv6_b200.h declares
 SYMBOLS = (
     "wkv6_b200_abi_version", "wkv6_b200_last_error", "wkv6_b200_launch_count", "wkv6_b200_set_algo",
-    "wkv6_b200_get_algo", "wkv6_b200_forward", "wkv6_b200_backward_workspace_bytes", "wkv6_b200_backward",
+    "wkv6_b200_get_algo", "wkv6_b200_checkpoint_bytes", "wkv6_b200_forward", "wkv6_b200_backward_workspace_bytes", "wkv6_b200_backward",
     "wkv6_b200_bi_forward", "wkv6_b200_bi_backward", "wkv6_b200_combine",
 )
 
@@ -41,15 +41,17 @@ def lib() -> ctypes.CDLL:
     L.wkv6_b200_launch_count.restype = ctypes.c_longlong
     L.wkv6_b200_set_algo.argtypes = [_i]
     L.wkv6_b200_get_algo.restype = _i
-    L.wkv6_b200_forward.argtypes = [_i] * 5 + [_vp] * 8 + [_i, _vp]
+    L.wkv6_b200_checkpoint_bytes.argtypes = [_i] * 4
+    L.wkv6_b200_checkpoint_bytes.restype = _sz
+    L.wkv6_b200_forward.argtypes = [_i] * 5 + [_vp] * 9 + [_i, _vp]
     L.wkv6_b200_forward.restype = _i
     L.wkv6_b200_backward_workspace_bytes.argtypes = [_i] * 6
     L.wkv6_b200_backward_workspace_bytes.restype = _sz
-    L.wkv6_b200_backward.argtypes = [_i] * 5 + [_vp] * 14 + [_i, _vp, _sz, _vp]
+    L.wkv6_b200_backward.argtypes = [_i] * 5 + [_vp] * 15 + [_i, _vp, _sz, _vp]
     L.wkv6_b200_backward.restype = _i
-    L.wkv6_b200_bi_forward.argtypes = [_i] * 5 + [_vp] * 16 + [_i, _vp]
+    L.wkv6_b200_bi_forward.argtypes = [_i] * 5 + [_vp] * 18 + [_i, _vp]
     L.wkv6_b200_bi_forward.restype = _i
-    L.wkv6_b200_bi_backward.argtypes = [_i] * 5 + [_vp] * 28 + [_i, _vp, _sz, _vp]
+    L.wkv6_b200_bi_backward.argtypes = [_i] * 5 + [_vp] * 30 + [_i, _vp, _sz, _vp]
     L.wkv6_b200_bi_backward.restype = _i
     L.wkv6_b200_combine.argtypes = [_i, _sz, _vp, _vp, ctypes.c_float, _i, _vp, _vp]
     L.wkv6_b200_combine.restype = _i

@@ -25,8 +25,11 @@ class _WKV6Base(torch.autograd.Function):
                 assert t.dtype == cls.DTYPE
                 assert t.is_contiguous()
             ctx.B, ctx.T, ctx.C, ctx.H = B, T, C, H
-            ctx.save_for_backward(r, k, v, w, u)
-            y, _ = ops.wkv6_forward_raw(r, k, v, w, u)
+            need = any(ctx.needs_input_grad)
+            ck = ops.checkpoint_buffer(r) if need else None
+            ctx.has_ck = ck is not None
+            ctx.save_for_backward(r, k, v, w, u, *((ck,) if ck is not None else ()))
+            y, _ = ops.wkv6_forward_raw(r, k, v, w, u, ckpt=ck)
             return y
 
     @classmethod
@@ -34,8 +37,9 @@ class _WKV6Base(torch.autograd.Function):
         with torch.no_grad():
             assert gy.dtype == cls.DTYPE
             gy = gy.contiguous()
-            r, k, v, w, u = ctx.saved_tensors
-            gr, gk, gv, gw, gu, _ = ops.wkv6_backward_raw(r, k, v, w, u, gy)
+            r, k, v, w, u = ctx.saved_tensors[:5]
+            ck = ctx.saved_tensors[5] if ctx.has_ck else None
+            gr, gk, gv, gw, gu, _ = ops.wkv6_backward_raw(r, k, v, w, u, gy, ckpt=ck)
             gu = torch.sum(gu, 0).view(ctx.H, ctx.C // ctx.H)      # model.py:151
             return gr, gk, gv, gw, gu
 
@@ -81,8 +85,10 @@ class WKV6State(torch.autograd.Function):
         with torch.no_grad():
             ctx.reverse = bool(reverse)
             ctx.has_s0 = s0 is not None
-            y, sT = ops.wkv6_forward_raw(r, k, v, w, u, s0=s0, reverse=reverse, want_state=True)
-            ctx.save_for_backward(r, k, v, w, u, *( (s0,) if s0 is not None else () ))
+            ck = ops.checkpoint_buffer(r) if any(ctx.needs_input_grad) else None
+            ctx.has_ck = ck is not None
+            y, sT = ops.wkv6_forward_raw(r, k, v, w, u, s0=s0, reverse=reverse, want_state=True, ckpt=ck)
+            ctx.save_for_backward(r, k, v, w, u, *((s0,) if s0 is not None else ()), *((ck,) if ck is not None else ()))
             ctx.H = u.shape[0]
             return y, sT
 
@@ -92,11 +98,12 @@ class WKV6State(torch.autograd.Function):
             saved = ctx.saved_tensors
             r, k, v, w, u = saved[:5]
             s0 = saved[5] if ctx.has_s0 else None
+            ck = saved[-1] if ctx.has_ck else None
             if gy is None:
                 gy = torch.zeros_like(r)
             gsT = None if gsT is None else gsT.contiguous().float()
             gr, gk, gv, gw, gu, gs0 = ops.wkv6_backward_raw(r, k, v, w, u, gy.contiguous(), s0=s0, gsT=gsT,
-                                                            reverse=ctx.reverse, want_gs0=ctx.has_s0)
+                                                            reverse=ctx.reverse, want_gs0=ctx.has_s0, ckpt=ck)
             gu = torch.sum(gu, 0).view(ctx.H, -1)
             return gr, gk, gv, gw, gu, gs0, None
 
@@ -115,8 +122,11 @@ class BiWKV6(torch.autograd.Function):
         with torch.no_grad():
             ctx.flags = int(flags)
             f, b = (r_f, k_f, v_f, w_f, u_f), (r_b, k_b, v_b, w_b, u_b)
-            y_f, y_b, _, _ = ops.bi_forward_raw(f, b, flags=ctx.flags)
-            ctx.save_for_backward(*f, *b)
+            run0 = f if (ctx.flags & _lib.BI_L2R) else b
+            ck = ops.checkpoint_buffer(run0[0], 2) if any(ctx.needs_input_grad) else None
+            ctx.has_ck = ck is not None
+            y_f, y_b, _, _ = ops.bi_forward_raw(f, b, flags=ctx.flags, ckpt=ck)
+            ctx.save_for_backward(*f, *b, *((ck,) if ck is not None else ()))
             run_f, run_b = bool(ctx.flags & _lib.BI_L2R), bool(ctx.flags & _lib.BI_R2L)
             ref = r_f if run_f else r_b
             # autograd wants tensors: a dropped direction yields an empty placeholder, marked non-differentiable
@@ -132,14 +142,15 @@ class BiWKV6(torch.autograd.Function):
     def backward(ctx, gy_f, gy_b):
         with torch.no_grad():
             t = ctx.saved_tensors
-            f, b = t[:5], t[5:]
+            f, b = t[:5], t[5:10]
+            ck = t[10] if ctx.has_ck else None
             flags = ctx.flags
             run_f, run_b = bool(flags & _lib.BI_L2R), bool(flags & _lib.BI_R2L)
             if run_f:
                 gy_f = (torch.zeros_like(f[0]) if gy_f is None else gy_f).contiguous()
             if run_b:
                 gy_b = (torch.zeros_like(b[0]) if gy_b is None else gy_b).contiguous()
-            of, ob = ops.bi_backward_raw(f, b, gy_f if run_f else None, gy_b if run_b else None, flags=flags)
+            of, ob = ops.bi_backward_raw(f, b, gy_f if run_f else None, gy_b if run_b else None, flags=flags, ckpt=ck)
             H = (f[4] if run_f else b[4]).shape[0]
 
             def pack(o, run):

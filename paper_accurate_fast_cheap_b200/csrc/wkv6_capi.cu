@@ -70,6 +70,24 @@ static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, in
     return 0;
 }
 
+// chunk-start state checkpoints: [B*H*nchunks*64 rows][64] bf16, box 64 x 64, 128B swizzle
+static int make_ckpt_map(CUtensorMap* m, const void* ptr, int B, int T, int H) {
+    encode_fn_t enc = get_encode();
+    if (!enc) return fail(WKV6_E_NODRIVER, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    const int nchunks = (T + 63) / 64;
+    const cuuint64_t dims[2] = {64u, (cuuint64_t)B * H * nchunks * 64};
+    const cuuint64_t strides[1] = {128u};
+    const cuuint32_t box[2] = {64u, 64u};
+    const cuuint32_t estr[2] = {1u, 1u};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(WKV6_E_BADARG, "cuTensorMapEncodeTiled(ckpt) failed with CUresult %d", (int)r);
+    return 0;
+}
+
+static size_t ckpt_bytes(int B, int T, int H) { return (size_t)B * H * ((T + 63) / 64) * 64 * 64 * 2; }
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 static int check_common(int dtype, int B, int T, int C, int H) {
@@ -84,6 +102,7 @@ struct FwdSet {
     const float* s0;
     void* y;
     float* sT;
+    void* ckpt;
 };
 struct BwdSet {
     const void *r, *k, *v, *w, *u;
@@ -92,6 +111,7 @@ struct BwdSet {
     const float* gsT;
     void *gr, *gk, *gv, *gw, *gu;
     float* gs0;
+    const void* ckpt;
 };
 
 static bool use_chunk(int dtype, int T) {
@@ -102,8 +122,9 @@ static bool use_chunk(int dtype, int T) {
     return true;    // AUTO and CHUNK: bf16 forward runs on the tcgen05 chunk kernel (2.3x the exact scan on cfg2)
 }
 
-static int fill_fwd(DirArgs& d, int dtype, int B, int T, int C, const FwdSet& s, int reverse, int rows, bool want_ymap) {
-    const void* ptrs[5] = {s.r, s.k, s.v, s.w, s.y};
+static int fill_fwd(DirArgs& d, int dtype, int B, int T, int C, const FwdSet& s, int reverse, int rows, bool want_ymap,
+                    bool skip_y = false) {
+    const void* ptrs[5] = {s.r, s.k, s.v, s.w, skip_y ? s.r : s.y};
     for (const void* q : ptrs)
         if (!q || !aligned16(q)) return fail(WKV6_E_BADARG, "forward: NULL or misaligned tensor pointer");
     if (!s.u) return fail(WKV6_E_BADARG, "forward: u is NULL");
@@ -113,7 +134,13 @@ static int fill_fwd(DirArgs& d, int dtype, int B, int T, int C, const FwdSet& s,
     if ((e = make_map(&d.mk, dtype, s.k, B, T, C, rows, want_ymap))) return e;
     if ((e = make_map(&d.mv, dtype, s.v, B, T, C, rows, want_ymap))) return e;
     if ((e = make_map(&d.mw, dtype, s.w, B, T, C, rows, want_ymap))) return e;
-    if (want_ymap && (e = make_map(&d.my, dtype, s.y, B, T, C, rows, true))) return e;
+    if (want_ymap && s.y && (e = make_map(&d.my, dtype, s.y, B, T, C, rows, true))) return e;
+    d.ckpt = nullptr;
+    if (want_ymap && s.ckpt) {
+        if (!aligned16(s.ckpt)) return fail(WKV6_E_BADARG, "forward: misaligned checkpoint buffer");
+        if ((e = make_ckpt_map(&d.mc, s.ckpt, B, T, C / N))) return e;
+        d.ckpt = s.ckpt;
+    }
     d.u = s.u; d.s0 = s.s0; d.sT = s.sT; d.y = s.y;
     d.reverse = reverse;
     return 0;
@@ -166,6 +193,53 @@ static int run_backward(int dtype, int B, int T, int C, int H, const BwdSet* set
     Params p;
     memset(&p, 0, sizeof(p));
     p.B = B; p.T = T; p.C = C; p.H = H; p.ndir = nset;
+    if (use_chunk(dtype, T)) {
+        // tcgen05 chunk backward: one reverse sweep over checkpoints of the chunk-start states.  Checkpoints come
+        // from the forward (ckpt argument) or are recomputed here into the workspace by a state-only forward.
+        const size_t cb = ckpt_bytes(B, T, H);
+        bool recompute = false;
+        Params pf;
+        memset(&pf, 0, sizeof(pf));
+        pf.B = B; pf.T = T; pf.C = C; pf.H = H; pf.ndir = 0; pf.skip_y = 1;
+        for (int i = 0; i < nset; i++) {
+            const BwdSet& s = sets[i];
+            DirArgs& d = p.d[i];
+            const void* ptrs[10] = {s.r, s.k, s.v, s.w, s.gy, s.gr, s.gk, s.gv, s.gw, s.gu};
+            for (const void* q : ptrs)
+                if (!q || !aligned16(q)) return fail(WKV6_E_BADARG, "backward: NULL or misaligned tensor pointer");
+            if (!s.u) return fail(WKV6_E_BADARG, "backward: u is NULL");
+            const void* ck = s.ckpt;
+            if (!ck) {
+                if (!ws || ws_bytes < cb * nset || !aligned16(ws))
+                    return fail(WKV6_E_WORKSPACE, "backward without checkpoints needs %zu workspace bytes", cb * nset);
+                void* mine = reinterpret_cast<char*>(ws) + cb * i;
+                const FwdSet fs = {s.r, s.k, s.v, s.w, s.u, s.s0, nullptr, nullptr, mine};
+                if ((e = fill_fwd(pf.d[pf.ndir], dtype, B, T, C, fs, reverse[i], 64, true, true))) return e;
+                pf.ndir++;
+                recompute = true;
+                ck = mine;
+            }
+            if ((e = make_map(&d.mr, dtype, s.r, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mk, dtype, s.k, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mv, dtype, s.v, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mw, dtype, s.w, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mg, dtype, s.gy, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mgr, dtype, s.gr, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mgk, dtype, s.gk, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mgv, dtype, s.gv, B, T, C, 64, true))) return e;
+            if ((e = make_map(&d.mgw, dtype, s.gw, B, T, C, 64, true))) return e;
+            if ((e = make_ckpt_map(&d.mc, ck, B, T, H))) return e;
+            d.ckpt = const_cast<void*>(ck);
+            d.u = s.u; d.s0 = s.s0; d.gsT = s.gsT; d.gs0 = s.gs0; d.gu = s.gu;
+            d.reverse = reverse[i];
+        }
+        if (recompute) {
+            e = launch_fwd_chunk(pf, (cudaStream_t)stream);
+            if (e) return cuda_fail(e, "wkv6 checkpoint recompute launch");
+        }
+        e = launch_bwd_chunk(p, (cudaStream_t)stream);
+        return cuda_fail(e, "wkv6 chunk backward launch");
+    }
     const size_t per_dir = (size_t)B * H * N * sizeof(float);
     for (int i = 0; i < nset; i++) {
         const BwdSet& s = sets[i];
@@ -204,15 +278,19 @@ using namespace wkv6;
 
 extern "C" {
 
-int wkv6_b200_abi_version(void) { return 1; }
+int wkv6_b200_abi_version(void) { return 2; }
+size_t wkv6_b200_checkpoint_bytes(int B, int T, int C, int H) {
+    (void)C;
+    return (B <= 0 || T <= 0 || H <= 0) ? 0 : ckpt_bytes(B, T, H);
+}
 const char* wkv6_b200_last_error(void) { return g_err; }
 long long wkv6_b200_launch_count(void) { return g_launches.load(); }
 void wkv6_b200_set_algo(int algo) { g_algo.store(algo); }
 int wkv6_b200_get_algo(void) { return g_algo.load(); }
 
 int wkv6_b200_forward(int dtype, int B, int T, int C, int H, const void* r, const void* k, const void* v, const void* w,
-                      const void* u, const float* s0, void* y, float* sT, int reverse, void* stream) {
-    const FwdSet s = {r, k, v, w, u, s0, y, sT};
+                      const void* u, const float* s0, void* y, float* sT, void* ckpt, int reverse, void* stream) {
+    const FwdSet s = {r, k, v, w, u, s0, y, sT, ckpt};
     const int rv = reverse != 0;
     return run_forward(dtype, B, T, C, H, &s, &rv, 1, stream);
 }
@@ -220,44 +298,49 @@ int wkv6_b200_forward(int dtype, int B, int T, int C, int H, const void* r, cons
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
     if (B <= 0 || H <= 0 || ndirections <= 0) return 0;
     size_t n = (size_t)ndirections * B * H * N * sizeof(float);                    /* hT  */
-    if (dtype == WKV6_DTYPE_BF16 && T > 0) n += (size_t)ndirections * B * T * C * 2;  /* grlo */
+    if (dtype == WKV6_DTYPE_BF16 && T > 0) {
+        n += (size_t)ndirections * B * T * C * 2;                                  /* grlo (exact scan)            */
+        const size_t c = (size_t)ndirections * ckpt_bytes(B, T, H);                /* checkpoints (chunk backward) */
+        if (c > n) n = c;
+    }
     return n;
 }
 
 int wkv6_b200_backward(int dtype, int B, int T, int C, int H, const void* r, const void* k, const void* v, const void* w,
-                       const void* u, const float* s0, const void* gy, const float* gsT, void* gr, void* gk, void* gv,
-                       void* gw, void* gu, float* gs0, int reverse, void* workspace, size_t workspace_bytes, void* stream) {
-    const BwdSet s = {r, k, v, w, u, s0, gy, gsT, gr, gk, gv, gw, gu, gs0};
+                       const void* u, const float* s0, const void* gy, const float* gsT, const void* ckpt, void* gr,
+                       void* gk, void* gv, void* gw, void* gu, float* gs0, int reverse, void* workspace,
+                       size_t workspace_bytes, void* stream) {
+    const BwdSet s = {r, k, v, w, u, s0, gy, gsT, gr, gk, gv, gw, gu, gs0, ckpt};
     const int rv = reverse != 0;
     return run_backward(dtype, B, T, C, H, &s, &rv, 1, workspace, workspace_bytes, stream);
 }
 
 int wkv6_b200_bi_forward(int dtype, int B, int T, int C, int H,
                          const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
-                         const float* s0_f, void* y_f, float* sT_f,
+                         const float* s0_f, void* y_f, float* sT_f, void* ckpt_f,
                          const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
-                         const float* s0_b, void* y_b, float* sT_b, int flags, void* stream) {
+                         const float* s0_b, void* y_b, float* sT_b, void* ckpt_b, int flags, void* stream) {
     FwdSet sets[2];
     int rv[2];
     int n = 0;
-    if (flags & WKV6_BI_L2R) { sets[n] = {r_f, k_f, v_f, w_f, u_f, s0_f, y_f, sT_f}; rv[n++] = 0; }
-    if (flags & WKV6_BI_R2L) { sets[n] = {r_b, k_b, v_b, w_b, u_b, s0_b, y_b, sT_b}; rv[n++] = 1; }
+    if (flags & WKV6_BI_L2R) { sets[n] = {r_f, k_f, v_f, w_f, u_f, s0_f, y_f, sT_f, ckpt_f}; rv[n++] = 0; }
+    if (flags & WKV6_BI_R2L) { sets[n] = {r_b, k_b, v_b, w_b, u_b, s0_b, y_b, sT_b, ckpt_b}; rv[n++] = 1; }
     return run_forward(dtype, B, T, C, H, sets, rv, n, stream);
 }
 
 int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
                           const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
-                          const float* s0_f, const void* gy_f, const float* gsT_f,
+                          const float* s0_f, const void* gy_f, const float* gsT_f, const void* ckpt_f,
                           void* gr_f, void* gk_f, void* gv_f, void* gw_f, void* gu_f, float* gs0_f,
                           const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
-                          const float* s0_b, const void* gy_b, const float* gsT_b,
+                          const float* s0_b, const void* gy_b, const float* gsT_b, const void* ckpt_b,
                           void* gr_b, void* gk_b, void* gv_b, void* gw_b, void* gu_b, float* gs0_b,
                           int flags, void* workspace, size_t workspace_bytes, void* stream) {
     BwdSet sets[2];
     int rv[2];
     int n = 0;
-    if (flags & WKV6_BI_L2R) { sets[n] = {r_f, k_f, v_f, w_f, u_f, s0_f, gy_f, gsT_f, gr_f, gk_f, gv_f, gw_f, gu_f, gs0_f}; rv[n++] = 0; }
-    if (flags & WKV6_BI_R2L) { sets[n] = {r_b, k_b, v_b, w_b, u_b, s0_b, gy_b, gsT_b, gr_b, gk_b, gv_b, gw_b, gu_b, gs0_b}; rv[n++] = 1; }
+    if (flags & WKV6_BI_L2R) { sets[n] = {r_f, k_f, v_f, w_f, u_f, s0_f, gy_f, gsT_f, gr_f, gk_f, gv_f, gw_f, gu_f, gs0_f, ckpt_f}; rv[n++] = 0; }
+    if (flags & WKV6_BI_R2L) { sets[n] = {r_b, k_b, v_b, w_b, u_b, s0_b, gy_b, gsT_b, gr_b, gk_b, gv_b, gw_b, gu_b, gs0_b, ckpt_b}; rv[n++] = 1; }
     return run_backward(dtype, B, T, C, H, sets, rv, n, workspace, workspace_bytes, stream);
 }
 

@@ -18,74 +18,9 @@
 // MN-major operands (conventions verified on hardware by tests/probes/umma_probe.cu).  Accumulators live in TMEM
 // (P^T, Y, dS^T: 3 x 64 columns) and are read with tcgen05.ld.16x256b; the fp32 state S^T[j][i] stays in
 // registers in that fragment layout for the whole sequence.
-#include "wkv6_scan.cuh"
+#include "wkv6_umma.cuh"
 
 namespace wkv6 {
-
-constexpr int CL = 64;                              // chunk length
-constexpr float kLog2e = 1.4426950408889634f;
-constexpr float kClampL2 = 5.0f * 1.4426950408889634f;   // per-step decay floor exp(-5) = 6.7e-3
-
-__device__ __forceinline__ float ex2(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3fff);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
-    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
-    d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
-    d |= (uint64_t)2 << 61;   // SWIZZLE_128B
-    return d;
-}
-__device__ __forceinline__ uint64_t desc_k(uint32_t saddr) { return umma_desc(saddr, 16, 1024); }     // K-major, +32 B per 16 k
-__device__ __forceinline__ uint64_t desc_mn(uint32_t saddr) { return umma_desc(saddr, 8192, 1024); }  // MN-major, +2048 B per 16 k
-
-// kind::f16 instruction descriptor: bf16 x bf16 -> fp32
-__host__ __device__ constexpr uint32_t umma_idesc(int a_mn, int b_mn, int M, int Nn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
-           ((uint32_t)(Nn >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-
-__device__ __forceinline__ void umma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-    asm volatile(
-        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// 16 TMEM lanes x 64 columns -> 32 registers per thread: reg 4*rep + 2*hh + e  <->  row (lane/4) + 8*hh,
-// column 8*rep + 2*(lane%4) + e
-__device__ __forceinline__ void tmem_ld_16x64(uint32_t taddr, float (&v)[32]) {
-    uint32_t u[32];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.16x256b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,"
-        "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]), "=r"(u[9]),
-          "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15]), "=r"(u[16]), "=r"(u[17]), "=r"(u[18]),
-          "=r"(u[19]), "=r"(u[20]), "=r"(u[21]), "=r"(u[22]), "=r"(u[23]), "=r"(u[24]), "=r"(u[25]), "=r"(u[26]), "=r"(u[27]),
-          "=r"(u[28]), "=r"(u[29]), "=r"(u[30]), "=r"(u[31])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 32; i++) v[i] = __uint_as_float(u[i]);
-}
-
-// byte offset of the 16-byte chunk `cg` of row `row` in a [rows][64] bf16 tile with the 128B swizzle
-__device__ __forceinline__ int sw_chunk(int row, int cg) { return row * 128 + ((cg ^ (row & 7)) << 4); }
-
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-}
 
 struct ChunkSmem {
     alignas(1024) uint8_t raw_r[CL * 128];   // TMA landing tiles (bf16, swizzled)
@@ -307,6 +242,10 @@ __global__ void __launch_bounds__(128, 2) wkv6_fwd_chunk_kernel(const __grid_con
         __syncthreads();   // B2: operand tiles complete
         if (tid == 0) {
             tc_fence_after();
+            if (D.ckpt) {   // S at the start of this chunk (bf16, [j][i]) -> checkpoint c of this sequence
+                tma_store_2d(&D.mc, sm.sp, 0, (bh * nchunks + c) * N);
+                tma_store_commit();
+            }
             mbar_wait(&sm.bar_v[c & 1], (c >> 1) & 1);
             const uint32_t a_rst = smem_u32(sm.rst), b_sp = smem_u32(sm.sp), a_kt = smem_u32(sm.kt), b_roff = smem_u32(sm.roff),
                            b_v = smem_u32(sm.v[c & 1]);
@@ -347,6 +286,7 @@ __global__ void __launch_bounds__(128, 2) wkv6_fwd_chunk_kernel(const __grid_con
         }
         fence_proxy_async();
         tc_fence_before();
+        if (tid == 0 && D.ckpt) tma_store_wait_read<0>();   // sp is rewritten after B3
         __syncthreads();   // B3: P^T tile complete
         if (tid == 0) {
             tc_fence_after();
@@ -388,7 +328,7 @@ __global__ void __launch_bounds__(128, 2) wkv6_fwd_chunk_kernel(const __grid_con
         fence_proxy_async();
         tc_fence_before();
         __syncthreads();   // B4: y tile complete; all TMEM reads of this chunk done
-        if (tid == 0) {
+        if (tid == 0 && !p.skip_y) {
             tma_store_3d(&D.my, sm.pt, h * N, t0, b);
             tma_store_commit();
         }

@@ -1,0 +1,679 @@
+// wkv6_chunk_bwd.cu -- chunked (dense-contraction) WKV6 backward for bf16 I/O on tcgen05 / TMEM / TMA (sm_100a).
+//
+// Same function as the reference's four backward kernels (wenet/rwkv_v6/cuda/wkv6_cuda.cu:66-263; with initial state
+// and gs: wkv6state_cuda.cu:68-293), restated per chunk of L = 64 steps so that all O(L*N*N) work is dense MMA.
+// ONE sweep against the direction's time order; the forward state at every chunk start comes from bf16 checkpoints
+// written by the chunked forward (wkv6_chunk.cu), the reverse state C[i][j] = sum_{p>t} (prod d) gy_p[i] r_p[j] is
+// carried in registers.  Notation (log2 domain): l_p = -exp(w_p) log2e, A_p = exclusive cumsum
+// in the chunk, A+_p = A_p + l_p, a_I = A at the start of 16-step sub-block I, A_L = chunk total.
+//
+//   Q[p][q]   = gy_p . v_q                                  (contraction over the value channel i)
+//   P[p][q]   = sum_j r_p k_q 2^(A_p - A+_q)   (q before p),   P[p][p] = sum_j r_p u k_p          (as in the forward)
+//   gv_q      = sum_p P[p][q] gy_p  +  sum_j k_q 2^(A_L - A+_q) C_L[.][j]
+//   gr_p[j]   = 2^(A_p - a_I) [ sum_{q<p} Q[p][q] k_q 2^(a_I - A+_q)  +  2^(a_I) sum_i gy_p[i] S_0[i][j] ] + u k_p (v_p.gy_p)
+//   gk_q[j]   = 2^(a_{J+1} - A+_q) [ sum_{p>q} Q[p][q] r_p 2^(A_p - a_{J+1}) + 2^(A_L - a_{J+1}) sum_i v_q[i] C_L[i][j] ]
+//               + u r_q (v_q.gy_q)
+//   C_0       = C_L 2^(A_L) + sum_p gy_p (r_p 2^(A_p))^T
+//   gw_p[j]   = -exp(w_p) H_p,   H_p = sum_i S_0[i][j] C_0[i][j] + sum_{q<p} (k_q gkC_q - r_q grS_q) - r_p grS_p
+// (grS / gkC = gr / gk without their u terms).  The last line is the reference's gw (kernel_backward_201) written as
+// a chunk-local prefix sum re-anchored at every chunk start by S_0 . C_0: no O(T) array, no T limit, and rounding
+// errors cannot accumulate beyond 64 steps.  Every exponent that reaches an MMA operand is relative to the start
+// (forward factors) or the end (gk factors) of the row's own 16-step sub-block: bounded by 2^115, finite in bf16.
+//
+// MMA groups per chunk (tcgen05.mma kind::f16, bf16 operands, fp32 accumulators in TMEM, one issuing thread):
+//   phase 1:  Q = G V^T;  P^T (4 x N16, as forward G1);  RS^T[j][p] = S0^T G^T;  KC^T[j][q] = C^T V^T
+//   phase 2:  R^T[j][p in I] = Ktil(I)^T Qm^T (4 x N16);  K^T[j][q in J] = Rtil'(J)^T Qm (4 x N16);
+//             GV[q][i] = P^T G + Kend C^T;  dC^T[j][i] = Rst^T G
+// 8 accumulators x 64 columns = all 512 TMEM columns -> one CTA (256 threads) per SM.
+#include "wkv6_umma.cuh"
+
+namespace wkv6 {
+
+constexpr int XSTR = 68;   // row stride (floats) of the fp32 transposition buffers: conflict-free scalar stores
+
+__device__ __forceinline__ void tmem_ld_16x32(uint32_t taddr, float (&v)[16]) {   // 16 lanes x 32 columns
+    uint32_t u[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]), "=r"(u[9]),
+          "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; i++) v[i] = __uint_as_float(u[i]);
+}
+
+__device__ __forceinline__ void ld4bf(const uint8_t* p, float (&f)[4]) {   // 4 consecutive bf16 -> fp32
+    const uint2 q = *reinterpret_cast<const uint2*>(p);
+    f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
+    f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
+}
+__device__ __forceinline__ void st4bf(uint8_t* p, const float (&f)[4]) {
+    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]));
+}
+// x = hi + lo with hi = bf16(x), lo = bf16(x - hi): two bf16 tiles carry ~16 mantissa bits through the MMA.  Needed
+// where two differently factorised sums must cancel (the gw prefix sum), see DESIGN.md.
+__device__ __forceinline__ void st4bf_hilo(uint8_t* hi, uint8_t* lo, const float (&f)[4]) {
+    const uint32_t h0 = pack_bf16(f[0], f[1]), h1 = pack_bf16(f[2], f[3]);
+    *reinterpret_cast<uint2*>(hi) = make_uint2(h0, h1);
+    const float l0 = f[0] - __uint_as_float(h0 << 16), l1 = f[1] - __uint_as_float(h0 & 0xffff0000u);
+    const float l2 = f[2] - __uint_as_float(h1 << 16), l3 = f[3] - __uint_as_float(h1 & 0xffff0000u);
+    *reinterpret_cast<uint2*>(lo) = make_uint2(pack_bf16(l0, l1), pack_bf16(l2, l3));
+}
+
+struct BwdChunkSmem {
+    alignas(1024) uint8_t raw_r[CL * 128];   // TMA landing tiles (bf16, 128B swizzle), rows = time, cols = channel
+    alignas(1024) uint8_t raw_k[CL * 128];
+    alignas(1024) uint8_t raw_w[CL * 128];
+    alignas(1024) uint8_t v[CL * 128];       // V and G: MMA operands straight from TMA
+    alignas(1024) uint8_t g[CL * 128];
+    alignas(1024) uint8_t sp[N * 128];       // S_0^T [j][i] bf16 (checkpoint, TMA)
+    alignas(1024) uint8_t cp[N * 128];       // C^T   [j][i] bf16 copy of the reverse state
+    alignas(1024) uint8_t roff[CL * 128];    // r 2^(A_p - a_I)
+    alignas(1024) uint8_t rst[CL * 128];     // r 2^(A_p)
+    alignas(1024) uint8_t rst_lo[CL * 128];  // low-order halves (see st4bf_hilo)
+    alignas(1024) uint8_t kt_lo[20 * 1024];
+    alignas(1024) uint8_t rp_lo[20 * 1024];
+    alignas(1024) uint8_t kt[28 * 1024];     // Ktil(0..3) compact (20 KB) + Kend (8 KB); later: fp32 buffer xr
+    alignas(1024) uint8_t rp[20 * 1024];     // Rtil'(0..3) compact; later: fp32 buffer xk
+    alignas(1024) uint8_t qm[CL * 128];      // masked Q   [p][q];   after the phase-2 MMAs: staging tile of gr
+    alignas(1024) uint8_t qmt[CL * 128];     // masked Q^T [q][p];   after the phase-2 MMAs: staging tile of gk
+    alignas(1024) uint8_t pt[CL * 128];      // masked P^T [q][p] with the u-bonus diagonal; later: staging tile of gv
+    alignas(1024) uint8_t o_gw[CL * 128];    // staging tile of gw (TMA store)
+    float blocktot[4][N];                    // log2 decay sums of the four sub-blocks (direction order), per channel
+    float dtot[4][N];                        // sub-block sums of (k gkC - r grS), per channel
+    float hst[2][N];                         // S_0 . C_0 partial sums (two column halves)
+    float bonus[2][CL];                      // sum_j r u k per row (two channel halves)
+    float vg[CL];                            // v_p . gy_p per row
+    float gured[8][N / 2];
+    alignas(8) uint64_t bar_in, bar_m1, bar_m2;
+    uint32_t tmem_base;
+};
+static_assert(sizeof(BwdChunkSmem) <= 226 * 1024, "shared memory budget");
+static_assert(CL * XSTR * 4 <= 20 * 1024, "xk must fit into the rp region");
+
+__global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_constant__ Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_bytes[];
+    BwdChunkSmem& sm = *reinterpret_cast<BwdChunkSmem*>((reinterpret_cast<uintptr_t>(smem_bytes) + 1023) & ~uintptr_t(1023));
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int BH = p.B * p.H;
+    const int ds = blockIdx.x / BH;
+    const int bh = blockIdx.x - ds * BH;
+    const int b = bh / p.H, h = bh - b * p.H;
+    const DirArgs& D = p.d[ds];
+    const bool rev = D.reverse != 0;
+    const int T = p.T;
+    const int nchunks = (T + CL - 1) / CL;
+
+    // compact variant tiles: virtual base (row 0) of every variant inside sm.kt / sm.rp
+    const int vbK[4] = {rev ? 12288 : 0, rev ? 10240 : 2048, 6144, rev ? 0 : 12288};   // Ktil(I): sub-blocks <= I
+    const int vbR[4] = {0, rev ? 8192 : 6144, rev ? 14336 : 10240, rev ? 18432 : 12288};   // Rtil'(J): sub-blocks >= J
+    uint8_t* const kend = sm.kt + 20 * 1024;
+    float* const xr = reinterpret_cast<float*>(sm.kt);   // [p][XSTR] fp32, valid after the phase-2 MMAs
+    float* const xk = reinterpret_cast<float*>(sm.rp);
+    uint8_t* const o_gr = sm.qm;    // staging tiles alias operand tiles that are dead after the phase-2 MMAs; the next
+    uint8_t* const o_gk = sm.qmt;   // chunk rewrites them only after thread 0 has waited for the TMA stores
+    uint8_t* const o_gv = sm.pt;
+
+    if (tid == 0) {
+        mbar_init(&sm.bar_in, 1);
+        mbar_init(&sm.bar_m1, 1);
+        mbar_init(&sm.bar_m2, 1);
+        fence_barrier_init();
+        tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
+        tma_prefetch_desc(&D.mg); tma_prefetch_desc(&D.mc);
+        tma_prefetch_desc(&D.mgr); tma_prefetch_desc(&D.mgk); tma_prefetch_desc(&D.mgv); tma_prefetch_desc(&D.mgw);
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    for (int i = tid; i < 28 * 1024 / 16; i += 256) reinterpret_cast<uint4*>(sm.kt)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < 20 * 1024 / 16; i += 256) reinterpret_cast<uint4*>(sm.rp)[i] = make_uint4(0, 0, 0, 0);
+
+    // ---- fragment coordinates (TMEM 16x256b.x4): rows frow, frow+8; columns fcol + 8*rep + {0,1}, rep = 0..3
+    const int qtr = warp & 3, half = warp >> 2;
+    const int frow = 16 * qtr + (lane >> 2);
+    const int fcol = 32 * half + 2 * (lane & 3);
+    const uint32_t lane_field = (uint32_t)(qtr * 32) << 16;
+
+    // ---- row-major coordinates (preprocessing / final epilogue): sub-block I (direction order), 4 rows x 4 channels
+    const int I = warp & 3, ch = warp >> 2;
+    const int cq = lane & 7, rg = lane >> 3;
+    const int c0 = 32 * ch + 4 * cq;
+    const int coff = (c0 & 7) * 2, cchunk = c0 >> 3;
+    const int vbK_own = I == 0 ? vbK[0] : I == 1 ? vbK[1] : I == 2 ? vbK[2] : vbK[3];
+
+    float u4[4];
+    ld4bf(reinterpret_cast<const uint8_t*>(D.u) + (h * N + c0) * 2, u4);
+    float gu4[4] = {0.f, 0.f, 0.f, 0.f};
+
+    // reverse state C^T[j][i]: j = frow + 8*hh, i = fcol + 8*rep + e  ->  cs[4*rep + 2*hh + e]
+    float cs[16];
+    {
+        const float* g0 = D.gsT ? D.gsT + (size_t)bh * N * N : nullptr;
+#pragma unroll
+        for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                for (int e = 0; e < 2; e++)
+                    cs[4 * rep + 2 * hh + e] = g0 ? g0[(fcol + 8 * rep + e) * N + frow + 8 * hh] : 0.f;
+    }
+    auto store_cp = [&]() {
+#pragma unroll
+        for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++) {
+                const int col = fcol + 8 * rep;
+                *reinterpret_cast<uint32_t*>(sm.cp + sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2) =
+                    pack_bf16(cs[4 * rep + 2 * hh], cs[4 * rep + 2 * hh + 1]);
+            }
+    };
+    store_cp();
+
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = sm.tmem_base;
+    const uint32_t tQ = tbase, tP = tbase + 64, tRS = tbase + 128, tKC = tbase + 192, tR = tbase + 256, tK = tbase + 320,
+                   tGV = tbase + 384, tDC = tbase + 448;
+
+    auto issue_tma = [&](int cb) {   // thread 0 only
+        const int c = nchunks - 1 - cb;
+        const int q = rev ? nchunks - 1 - c : c;
+        mbar_arrive_expect_tx(&sm.bar_in, 6u * CL * 128);
+        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_in, h * N, q * CL, b);
+        tma_load_3d(sm.raw_k, &D.mk, &sm.bar_in, h * N, q * CL, b);
+        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_in, h * N, q * CL, b);
+        tma_load_3d(sm.v, &D.mv, &sm.bar_in, h * N, q * CL, b);
+        tma_load_3d(sm.g, &D.mg, &sm.bar_in, h * N, q * CL, b);
+        tma_load_2d(sm.sp, &D.mc, &sm.bar_in, 0, (bh * nchunks + c) * N);
+    };
+    if (tid == 0 && nchunks > 0) issue_tma(0);
+
+    constexpr uint32_t ID_KK64 = umma_idesc(0, 0, 64, 64);
+    constexpr uint32_t ID_KK16 = umma_idesc(0, 0, 64, 16);
+    constexpr uint32_t ID_MK16 = umma_idesc(1, 0, 64, 16);
+    constexpr uint32_t ID_KM64 = umma_idesc(0, 1, 64, 64);
+    constexpr uint32_t ID_MM64 = umma_idesc(1, 1, 64, 64);
+
+    for (int cb = 0; cb < nchunks; cb++) {
+        const int c = nchunks - 1 - cb;                  // chunk index in the direction's own order
+        const int q = rev ? nchunks - 1 - c : c;         // tile index in memory
+        const int t0 = q * CL;
+        const uint32_t par = cb & 1;
+        if (tid == 0) tma_store_wait_read<0>();          // staging tiles of the previous chunk have been read
+
+        // ================= phase 1: decays, in-block cumulative sums, Rtil, Ktil(own), bonus
+        mbar_wait(&sm.bar_in, par);
+        float eo[4][4], ei[4][4], ew[4][4], bt[4];
+        int rows[4];
+        {
+            float rr[4][4], kk[4][4], l2[4][4], bsum[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int pos = 16 * I + 4 * rg + r;
+                const int row = rev ? 63 - pos : pos;
+                rows[r] = row;
+                const int off = sw_chunk(row, cchunk) + coff;
+                float w4[4];
+                ld4bf(sm.raw_r + off, rr[r]);
+                ld4bf(sm.raw_k + off, kk[r]);
+                ld4bf(sm.raw_w + off, w4);
+                const bool valid = t0 + row < T;
+                float bs = 0.f;
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    bs = fmaf(rr[r][e] * u4[e], kk[r][e], bs);
+                    const float x = ex2(w4[e] * kLog2e);            // exp(w)
+                    ew[r][e] = x;
+                    const float l = fmaxf(-x * kLog2e, -kClampL2);
+                    l2[r][e] = valid ? l : 0.f;
+                }
+                bsum[r] = bs;
+            }
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                l2[1][e] += l2[0][e];
+                l2[2][e] += l2[1][e];
+                l2[3][e] += l2[2][e];
+            }
+            float excl[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                float x = l2[3][e];
+                float y = __shfl_up_sync(0xffffffffu, x, 8);
+                if (rg >= 1) x += y;
+                y = __shfl_up_sync(0xffffffffu, x, 16);
+                if (rg >= 2) x += y;
+                excl[e] = x - l2[3][e];
+                if (rg == 3) sm.blocktot[I][c0 + e] = x;
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                float ro[4], ko[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float aex = excl[e] + (r ? l2[r - 1][e] : 0.f);   // A_p  - a_I   (<= 0)
+                    const float ain = excl[e] + l2[r][e];                   // A+_p - a_I   (<= 0)
+                    eo[r][e] = ex2(aex);
+                    ei[r][e] = ex2(-ain);
+                    ro[e] = rr[r][e] * eo[r][e];
+                    ko[e] = kk[r][e] * ei[r][e];
+                }
+                const int off = sw_chunk(rows[r], cchunk) + coff;
+                st4bf(sm.roff + off, ro);
+                st4bf_hilo(sm.kt + vbK_own + off, sm.kt_lo + vbK_own + off, ko);
+                float bs = bsum[r];
+                bs += __shfl_xor_sync(0xffffffffu, bs, 1);
+                bs += __shfl_xor_sync(0xffffffffu, bs, 2);
+                bs += __shfl_xor_sync(0xffffffffu, bs, 4);
+                if (cq == 0) sm.bonus[ch][rows[r]] = bs;
+            }
+        }
+        __syncthreads();   // B1: blocktot / bonus visible
+
+        // ================= phase 1b: cross-block factors -> Rst, Ktil(I' > I), Kend, Rtil'(J <= I)
+        {
+            float tot[4][4];   // blocktot[m][c0 + e]
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                const float4 t = *reinterpret_cast<const float4*>(&sm.blocktot[m][c0]);
+                tot[m][0] = t.x; tot[m][1] = t.y; tot[m][2] = t.z; tot[m][3] = t.w;
+            }
+            float fst[4], fk[4][4], fr[4][4];   // 2^(a_I);  fk[I'] = 2^(a_I' - a_I) (I' = 4: chunk end);  fr[J] = 2^(a_I - a_{J+1})
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                float s = 0.f;
+#pragma unroll
+                for (int m = 0; m < 4; m++)
+                    if (m < I) s += tot[m][e];
+                fst[e] = ex2(s);
+                bt[e] = tot[0][e];
+#pragma unroll
+                for (int m = 1; m < 4; m++)
+                    if (m == I) bt[e] = tot[m][e];
+                float acc = 0.f;
+#pragma unroll
+                for (int m = 0; m < 4; m++) {       // fk[m] for target I' = m + 1
+                    if (m >= I) acc += tot[m][e];
+                    fk[m][e] = ex2(acc);
+                }
+                // fr[J], J <= I: exponent a_I - a_{J+1} = -bt (J = I), 0 (J = I-1), sum_{m=J+1}^{I-1} tot[m] otherwise
+                float acr = 0.f;
+#pragma unroll
+                for (int J = 3; J >= 0; J--) {
+                    if (J == I) fr[J][e] = ex2(-bt[e]);
+                    else if (J < I) {
+                        fr[J][e] = ex2(acr);
+                        acr += tot[J][e];       // the next (smaller) J also crosses sub-block J
+                    } else fr[J][e] = 0.f;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int off = sw_chunk(rows[r], cchunk) + coff;
+                float ro[4], ko[4], x4[4];
+                ld4bf(sm.raw_r + off, ro);
+                ld4bf(sm.raw_k + off, ko);
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    ro[e] *= eo[r][e];
+                    ko[e] *= ei[r][e];
+                    x4[e] = ro[e] * fst[e];
+                }
+                st4bf_hilo(sm.rst + off, sm.rst_lo + off, x4);
+#pragma unroll
+                for (int m = 0; m < 4; m++) {
+                    if (m >= I) {               // target variant I' = m + 1 (I' = 4 -> Kend)
+#pragma unroll
+                        for (int e = 0; e < 4; e++) x4[e] = ko[e] * fk[m][e];
+                        if (m == 3) st4bf(kend + off, x4);
+                        else st4bf_hilo(sm.kt + vbK[m + 1] + off, sm.kt_lo + vbK[m + 1] + off, x4);
+                    }
+                }
+#pragma unroll
+                for (int J = 0; J < 4; J++) {
+                    if (J <= I) {
+#pragma unroll
+                        for (int e = 0; e < 4; e++) x4[e] = ro[e] * fr[J][e];
+                        st4bf_hilo(sm.rp + vbR[J] + off, sm.rp_lo + vbR[J] + off, x4);
+                    }
+                }
+            }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();   // B2: operand tiles complete
+
+        // ================= MMA phase 1
+        if (tid == 0) {
+            tc_fence_after();
+            const uint32_t a_g = smem_u32(sm.g), a_v = smem_u32(sm.v), a_kt = smem_u32(sm.kt), a_roff = smem_u32(sm.roff),
+                           a_sp = smem_u32(sm.sp), a_cp = smem_u32(sm.cp);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tQ, desc_k(a_g + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int rowlo = rev ? 48 - 16 * i : 16 * i;
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++)
+                    umma(tP + rowlo, desc_k(a_kt + vbK[i] + ks * 32), desc_k(a_roff + rowlo * 128 + ks * 32), ID_KK16, ks > 0);
+            }
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tRS, desc_k(a_sp + ks * 32), desc_k(a_g + ks * 32), ID_KK64, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tKC, desc_k(a_cp + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
+            umma_commit(&sm.bar_m1);
+        }
+
+        // ================= E1: Q -> masked Q, Q^T, vg;  P^T -> masked P^T with the bonus diagonal
+        mbar_wait(&sm.bar_m1, par);
+        tc_fence_after();
+        {
+            float x[16];
+            tmem_ld_16x32(tQ + lane_field + 32 * half, x);
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) {
+                    const int pp = frow + 8 * hh;
+                    float y[2];
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int qq = fcol + 8 * rep + e;
+                        const bool before = rev ? (qq > pp) : (qq < pp);
+                        const float val = x[4 * rep + 2 * hh + e];
+                        y[e] = before ? val : 0.f;
+                        if (qq == pp) sm.vg[pp] = val;
+                        *reinterpret_cast<__nv_bfloat16*>(sm.qmt + sw_chunk(qq, pp >> 3) + (pp & 7) * 2) = __float2bfloat16_rn(y[e]);
+                    }
+                    const int qc = fcol + 8 * rep;
+                    *reinterpret_cast<uint32_t*>(sm.qm + sw_chunk(pp, qc >> 3) + (qc & 7) * 2) = pack_bf16(y[0], y[1]);
+                }
+            tmem_ld_16x32(tP + lane_field + 32 * half, x);
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) {
+                    const int qq = frow + 8 * hh;
+                    float y[2];
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int pp = fcol + 8 * rep + e;
+                        const bool before = rev ? (qq > pp) : (qq < pp);
+                        y[e] = before ? x[4 * rep + 2 * hh + e] : (qq == pp ? sm.bonus[0][pp] + sm.bonus[1][pp] : 0.f);
+                    }
+                    const int pc = fcol + 8 * rep;
+                    *reinterpret_cast<uint32_t*>(sm.pt + sw_chunk(qq, pc >> 3) + (pc & 7) * 2) = pack_bf16(y[0], y[1]);
+                }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();   // B3: masked tiles complete
+
+        // ================= MMA phase 2
+        if (tid == 0) {
+            tc_fence_after();
+            const uint32_t a_g = smem_u32(sm.g), a_kt = smem_u32(sm.kt), a_rp = smem_u32(sm.rp), a_qm = smem_u32(sm.qm),
+                           a_qmt = smem_u32(sm.qmt), a_pt = smem_u32(sm.pt), a_kend = smem_u32(kend), a_cp = smem_u32(sm.cp),
+                           a_rst = smem_u32(sm.rst), a_rstl = smem_u32(sm.rst_lo), a_ktl = smem_u32(sm.kt_lo),
+                           a_rpl = smem_u32(sm.rp_lo);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {      // R^T[j][p in sub-block i] = sum over q in sub-blocks <= i
+                const int rb = rev ? 3 - i : i;
+#pragma unroll
+                for (int s = 0; s <= i; s++) {
+                    const int kb = rev ? 3 - s : s;
+                    umma(tR + 16 * rb, desc_mn(a_kt + vbK[i] + kb * 2048), desc_k(a_qm + rb * 2048 + kb * 32), ID_MK16, s > 0);
+                    umma(tR + 16 * rb, desc_mn(a_ktl + vbK[i] + kb * 2048), desc_k(a_qm + rb * 2048 + kb * 32), ID_MK16, 1);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {      // K^T[j][q in sub-block j] = sum over p in sub-blocks >= j
+                const int rb = rev ? 3 - j : j;
+#pragma unroll
+                for (int s = j; s < 4; s++) {
+                    const int kb = rev ? 3 - s : s;
+                    umma(tK + 16 * rb, desc_mn(a_rp + vbR[j] + kb * 2048), desc_k(a_qmt + rb * 2048 + kb * 32), ID_MK16, s > j);
+                    umma(tK + 16 * rb, desc_mn(a_rpl + vbR[j] + kb * 2048), desc_k(a_qmt + rb * 2048 + kb * 32), ID_MK16, 1);
+                }
+            }
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tGV, desc_k(a_pt + ks * 32), desc_mn(a_g + ks * 2048), ID_KM64, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tGV, desc_k(a_kend + ks * 32), desc_mn(a_cp + ks * 2048), ID_KM64, 1);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tDC, desc_mn(a_rst + ks * 2048), desc_mn(a_g + ks * 2048), ID_MM64, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tDC, desc_mn(a_rstl + ks * 2048), desc_mn(a_g + ks * 2048), ID_MM64, 1);
+            umma_commit(&sm.bar_m2);
+        }
+
+        // ================= E2: drain the phase-2 accumulators
+        mbar_wait(&sm.bar_m2, par);
+        tc_fence_after();
+        {
+            // per-thread decay factors of its two rows j (log2 sums of the sub-block totals)
+            float t0j[4], t1j[4];
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                t0j[m] = sm.blocktot[m][frow];
+                t1j[m] = sm.blocktot[m][frow + 8];
+            }
+            // columns of this thread lie in row-blocks 2*half and 2*half+1 -> sub-blocks (direction order) iA, iB
+            const int rbA = 2 * half, rbB = 2 * half + 1;
+            const int iA = rev ? 3 - rbA : rbA, iB = rev ? 3 - rbB : rbB;
+            float sR[2][2], sK[2][2];   // [row hh][block A/B]: 2^(a_I) and 2^(A_L - a_{I+1})
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++) {
+                const float* tj = hh ? t1j : t0j;
+                float preA = 0.f, preB = 0.f, sufA = 0.f, sufB = 0.f;
+#pragma unroll
+                for (int m = 0; m < 4; m++) {
+                    if (m < iA) preA += tj[m];
+                    if (m < iB) preB += tj[m];
+                    if (m > iA) sufA += tj[m];
+                    if (m > iB) sufB += tj[m];
+                }
+                sR[hh][0] = ex2(preA); sR[hh][1] = ex2(preB);
+                sK[hh][0] = ex2(sufA); sK[hh][1] = ex2(sufB);
+            }
+            float x[16], y[16];
+            tmem_ld_16x32(tR + lane_field + 32 * half, x);
+            tmem_ld_16x32(tRS + lane_field + 32 * half, y);
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int pp = fcol + 8 * rep + e, jj = frow + 8 * hh;
+                        xr[pp * XSTR + jj] = fmaf(sR[hh][rep >> 1], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
+                    }
+            tmem_ld_16x32(tK + lane_field + 32 * half, x);
+            tmem_ld_16x32(tKC + lane_field + 32 * half, y);
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int qq = fcol + 8 * rep + e, jj = frow + 8 * hh;
+                        xk[qq * XSTR + jj] = fmaf(sK[hh][rep >> 1], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
+                    }
+            // gv tile [q][i]
+            tmem_ld_16x32(tGV + lane_field + 32 * half, x);
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) {
+                    const int col = fcol + 8 * rep;
+                    *reinterpret_cast<uint32_t*>(o_gv + sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2) =
+                        pack_bf16(x[4 * rep + 2 * hh], x[4 * rep + 2 * hh + 1]);
+                }
+            // reverse state: C <- C 2^(A_L[j]) + dC;  then the anchor  hst[j] = sum_i S_0[i][j] C_0[i][j]
+            tmem_ld_16x32(tDC + lane_field + 32 * half, x);
+            const float f0 = ex2(t0j[0] + t0j[1] + t0j[2] + t0j[3]);
+            const float f1 = ex2(t1j[0] + t1j[1] + t1j[2] + t1j[3]);
+            float h0 = 0.f, h1 = 0.f;
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++) {
+                cs[4 * rep + 0] = fmaf(cs[4 * rep + 0], f0, x[4 * rep + 0]);
+                cs[4 * rep + 1] = fmaf(cs[4 * rep + 1], f0, x[4 * rep + 1]);
+                cs[4 * rep + 2] = fmaf(cs[4 * rep + 2], f1, x[4 * rep + 2]);
+                cs[4 * rep + 3] = fmaf(cs[4 * rep + 3], f1, x[4 * rep + 3]);
+                const int col = fcol + 8 * rep;
+                const uint32_t s0w = *reinterpret_cast<const uint32_t*>(sm.sp + sw_chunk(frow, col >> 3) + (col & 7) * 2);
+                const uint32_t s1w = *reinterpret_cast<const uint32_t*>(sm.sp + sw_chunk(frow + 8, col >> 3) + (col & 7) * 2);
+                h0 = fmaf(__uint_as_float(s0w << 16), cs[4 * rep + 0], h0);
+                h0 = fmaf(__uint_as_float(s0w & 0xffff0000u), cs[4 * rep + 1], h0);
+                h1 = fmaf(__uint_as_float(s1w << 16), cs[4 * rep + 2], h1);
+                h1 = fmaf(__uint_as_float(s1w & 0xffff0000u), cs[4 * rep + 3], h1);
+            }
+            h0 += __shfl_xor_sync(0xffffffffu, h0, 1);
+            h0 += __shfl_xor_sync(0xffffffffu, h0, 2);
+            h1 += __shfl_xor_sync(0xffffffffu, h1, 1);
+            h1 += __shfl_xor_sync(0xffffffffu, h1, 2);
+            if ((lane & 3) == 0) {
+                sm.hst[half][frow] = h0;
+                sm.hst[half][frow + 8] = h1;
+            }
+            store_cp();
+        }
+        __syncthreads();   // B4: xr / xk / hst / vg visible; all TMEM reads of this chunk done
+
+        // ================= final epilogue (row-major): gr, gk, gu, gw
+        {
+            float dl[4][4], av[4][4];   // delta = k gkC - r grS,  a = r grS
+            const float4 hA = *reinterpret_cast<const float4*>(&sm.hst[0][c0]);
+            const float4 hB = *reinterpret_cast<const float4*>(&sm.hst[1][c0]);
+            const float hs[4] = {hA.x + hB.x, hA.y + hB.y, hA.z + hB.z, hA.w + hB.w};
+            float ebt[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) ebt[e] = ex2(bt[e]);
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int row = rows[r];
+                const int off = sw_chunk(row, cchunk) + coff;
+                float rr[4], kk[4], gr4[4], gk4[4];
+                ld4bf(sm.raw_r + off, rr);
+                ld4bf(sm.raw_k + off, kk);
+                const float vg = sm.vg[row];
+                const float4 a4 = *reinterpret_cast<const float4*>(&xr[row * XSTR + c0]);
+                const float4 b4 = *reinterpret_cast<const float4*>(&xk[row * XSTR + c0]);
+                const float xa[4] = {a4.x, a4.y, a4.z, a4.w}, xb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float grS = eo[r][e] * xa[e];
+                    const float gkC = ei[r][e] * ebt[e] * xb[e];
+                    gr4[e] = fmaf(u4[e] * kk[e], vg, grS);
+                    gk4[e] = fmaf(u4[e] * rr[e], vg, gkC);
+                    gu4[e] = fmaf(rr[e] * kk[e], vg, gu4[e]);
+                    av[r][e] = rr[e] * grS;
+                    dl[r][e] = fmaf(kk[e], gkC, -av[r][e]);
+                }
+                st4bf(o_gr + off, gr4);
+                st4bf(o_gk + off, gk4);
+            }
+            // exclusive prefix of delta over the chunk in direction order: thread (4 rows) -> row groups -> sub-blocks
+            float pre[4][4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                pre[0][e] = 0.f;
+                pre[1][e] = dl[0][e];
+                pre[2][e] = pre[1][e] + dl[1][e];
+                pre[3][e] = pre[2][e] + dl[2][e];
+                const float tot = pre[3][e] + dl[3][e];
+                float x = tot;
+                float y = __shfl_up_sync(0xffffffffu, x, 8);
+                if (rg >= 1) x += y;
+                y = __shfl_up_sync(0xffffffffu, x, 16);
+                if (rg >= 2) x += y;
+                const float ex = x - tot;
+#pragma unroll
+                for (int r = 0; r < 4; r++) pre[r][e] += ex;
+                if (rg == 3) sm.dtot[I][c0 + e] = x;
+            }
+            __syncthreads();   // B5: dtot visible
+            float base[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                float s = hs[e];
+#pragma unroll
+                for (int m = 0; m < 4; m++)
+                    if (m < I) s += sm.dtot[m][c0 + e];
+                base[e] = s;
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int row = rows[r];
+                const int t = t0 + row;
+                // exact zeros the reference hard-codes (wkv6_cuda.cu:237,262): nothing precedes the direction's first
+                // step when S_0 = 0, nothing follows its last step when no gradient enters S_T
+                const bool first = !D.s0 && (rev ? t == T - 1 : t == 0);
+                const bool last = !D.gsT && (rev ? t == 0 : t == T - 1);
+                float gw4[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float H = base[e] + pre[r][e] - av[r][e];
+                    gw4[e] = (first || last) ? 0.f : -ew[r][e] * H;
+                }
+                st4bf(sm.o_gw + sw_chunk(row, cchunk) + coff, gw4);
+            }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();   // B6: staging tiles complete; raw tiles and xr/xk no longer needed
+        if (tid == 0) {
+            tma_store_3d(&D.mgr, o_gr, h * N, t0, b);
+            tma_store_3d(&D.mgk, o_gk, h * N, t0, b);
+            tma_store_3d(&D.mgv, o_gv, h * N, t0, b);
+            tma_store_3d(&D.mgw, sm.o_gw, h * N, t0, b);
+            tma_store_commit();
+            if (cb + 1 < nchunks) issue_tma(cb + 1);
+        }
+    }
+
+    if (tid == 0) tma_store_wait<0>();
+    // gu[b][h*64 + c] = sum over rows of r k (v.gy): row groups by shuffle, sub-blocks through smem
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+        gu4[e] += __shfl_xor_sync(0xffffffffu, gu4[e], 8);
+        gu4[e] += __shfl_xor_sync(0xffffffffu, gu4[e], 16);
+    }
+    if (rg == 0) {
+#pragma unroll
+        for (int e = 0; e < 4; e++) sm.gured[warp][4 * cq + e] = gu4[e];
+    }
+    if (D.gs0) {
+        float* g0 = D.gs0 + (size_t)bh * N * N;
+#pragma unroll
+        for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) g0[(fcol + 8 * rep + e) * N + frow + 8 * hh] = cs[4 * rep + 2 * hh + e];
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (tid < N) {
+        const int hc = tid >> 5, cc = tid & 31;
+        const float g = sm.gured[4 * hc + 0][cc] + sm.gured[4 * hc + 1][cc] + sm.gured[4 * hc + 2][cc] + sm.gured[4 * hc + 3][cc];
+        reinterpret_cast<__nv_bfloat16*>(D.gu)[(size_t)b * p.C + h * N + tid] = __float2bfloat16_rn(g);
+    }
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
+}
+
+int launch_bwd_chunk(const Params& p, cudaStream_t st) {
+    const size_t smem = sizeof(BwdChunkSmem) + 1024;
+    cudaError_t e = cudaFuncSetAttribute(wkv6_bwd_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    wkv6_bwd_chunk_kernel<<<dim3(p.ndir * p.B * p.H), dim3(256), smem, st>>>(p);
+    count_launch(1);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace wkv6

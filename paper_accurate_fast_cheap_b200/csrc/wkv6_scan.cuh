@@ -11,6 +11,9 @@ constexpr int NT = 128;   // threads per CTA of the exact scan kernels (one CTA 
 struct alignas(64) DirArgs {
     CUtensorMap mr, mk, mv, mw, mg, mq;   // r, k, v, w, gy, gr(as input of pass B)
     CUtensorMap my;                       // y (TMA store; chunk kernel only)
+    CUtensorMap mc;                       // chunk-start state checkpoints, 2-D [B*H*nchunks*64][64] bf16 (chunk kernels)
+    CUtensorMap mgr, mgk, mgv, mgw;       // gradient outputs (TMA store; chunk backward only)
+    void* ckpt;                           // null: the forward does not save checkpoints
     const void* u;                        // [H,64] io dtype
     const float* s0;                      // [B,H,64,64] or null
     float* sT;                            // [B,H,64,64] or null
@@ -30,12 +33,14 @@ struct Params {
     DirArgs d[2];
     int B, T, C, H;
     int ndir;
+    int skip_y;                           // chunk forward: compute states/checkpoints only (backward recompute)
 };
 
 // launchers (wkv6_scan.cu / wkv6_chunk.cu); return cudaError_t as int
 int launch_fwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_bwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_fwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05
+int launch_bwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05; needs DirArgs::ckpt
 int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out, cudaStream_t st);
 
 void count_launch(int n);

@@ -30,7 +30,7 @@ void fwd_impl(int dtype, at::ScalarType dt, int64_t B, int64_t T, int64_t C, int
     TORCH_CHECK(u.is_cuda() && u.scalar_type() == dt && u.is_contiguous() && u.numel() == C, "wkv6: bad u");
     const c10::cuda::CUDAGuard guard(r.device());
     check_rc(wkv6_b200_forward(dtype, (int)B, (int)T, (int)C, (int)H, r.data_ptr(), k.data_ptr(), v.data_ptr(),
-                               w.data_ptr(), u.data_ptr(), nullptr, y.data_ptr(), nullptr, 0,
+                               w.data_ptr(), u.data_ptr(), nullptr, y.data_ptr(), nullptr, nullptr, 0,
                                at::cuda::getCurrentCUDAStream().stream()));
 }
 
@@ -46,7 +46,7 @@ void bwd_impl(int dtype, at::ScalarType dt, int64_t B, int64_t T, int64_t C, int
     const size_t ws_bytes = wkv6_b200_backward_workspace_bytes(dtype, (int)B, (int)T, (int)C, (int)H, 1);
     at::Tensor ws = at::empty({(int64_t)ws_bytes}, r.options().dtype(at::kByte));   // caching allocator, stream-ordered
     check_rc(wkv6_b200_backward(dtype, (int)B, (int)T, (int)C, (int)H, r.data_ptr(), k.data_ptr(), v.data_ptr(),
-                                w.data_ptr(), u.data_ptr(), nullptr, gy.data_ptr(), nullptr, gr.data_ptr(),
+                                w.data_ptr(), u.data_ptr(), nullptr, gy.data_ptr(), nullptr, nullptr, gr.data_ptr(),
                                 gk.data_ptr(), gv.data_ptr(), gw.data_ptr(), gu.data_ptr(), nullptr, 0, ws.data_ptr(),
                                 ws_bytes, at::cuda::getCurrentCUDAStream().stream()));
 }

@@ -55,18 +55,27 @@ def _check_state(s, B, H, dev):
 # --------------------------------------------------------------------------------------------------
 # raw (no autograd) calls into the C ABI
 # --------------------------------------------------------------------------------------------------
-def wkv6_forward_raw(r, k, v, w, u, s0=None, reverse=False, want_state=False):
+def checkpoint_buffer(r, ndir=1):
+    """Buffer for the chunk-start state checkpoints of `ndir` directions (bf16 tcgen05 path only), or None."""
+    if r.dtype != torch.bfloat16 or _lib.lib().wkv6_b200_get_algo() == _lib.ALGO_SCAN or r.size(1) == 0:
+        return None
+    B, T, C = r.size()
+    nb = _lib.lib().wkv6_b200_checkpoint_bytes(B, T, C, C // HEAD_SIZE)
+    return torch.empty((ndir, nb), device=r.device, dtype=torch.uint8)
+
+
+def wkv6_forward_raw(r, k, v, w, u, s0=None, reverse=False, want_state=False, ckpt=None):
     B, T, C, H = _check_inputs(r, k, v, w, u)
     _check_state(s0, B, H, r.device)
     y = torch.empty_like(r)
     sT = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_state else None
     with torch.cuda.device(r.device):
         _lib.check(_lib.lib().wkv6_b200_forward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u),
-                                                _p(s0), _p(y), _p(sT), int(bool(reverse)), _stream(r)))
+                                                _p(s0), _p(y), _p(sT), _p(ckpt), int(bool(reverse)), _stream(r)))
     return y, sT
 
 
-def wkv6_backward_raw(r, k, v, w, u, gy, s0=None, gsT=None, reverse=False, want_gs0=False):
+def wkv6_backward_raw(r, k, v, w, u, gy, s0=None, gsT=None, reverse=False, want_gs0=False, ckpt=None):
     """Returns gr, gk, gv, gw [B,T,C], gu [B,C] (per-batch partials, like the reference), gs0 or None."""
     B, T, C, H = _check_inputs(r, k, v, w, u, extra=(gy,))
     _check_state(s0, B, H, r.device)
@@ -75,16 +84,16 @@ def wkv6_backward_raw(r, k, v, w, u, gy, s0=None, gsT=None, reverse=False, want_
     gu = torch.empty((B, C), device=r.device, dtype=r.dtype)
     gs0 = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_gs0 else None
     L = _lib.lib()
-    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, 1)
+    ws_bytes = 0 if ckpt is not None else L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, 1)
     ws = torch.empty(ws_bytes, device=r.device, dtype=torch.uint8) if ws_bytes else None
     with torch.cuda.device(r.device):
         _lib.check(L.wkv6_b200_backward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u), _p(s0),
-                                        _p(gy), _p(gsT), _p(gr), _p(gk), _p(gv), _p(gw), _p(gu), _p(gs0),
+                                        _p(gy), _p(gsT), _p(ckpt), _p(gr), _p(gk), _p(gv), _p(gw), _p(gu), _p(gs0),
                                         int(bool(reverse)), _p(ws), ws_bytes, _stream(r)))
     return gr, gk, gv, gw, gu, gs0
 
 
-def bi_forward_raw(f, b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, want_state=False):
+def bi_forward_raw(f, b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, want_state=False, ckpt=None):
     """f, b: (r, k, v, w, u) of the L2R / R2L direction.  One launch.  Returns (y_f, y_b, sT_f, sT_b);
     outputs of a direction whose flag bit is clear are None."""
     ref = f if (flags & _lib.BI_L2R) else b
@@ -103,15 +112,18 @@ def bi_forward_raw(f, b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, 
     none5 = (None,) * 5
     fa = tuple(_p(t) for t in f) if run_f else none5
     ba = tuple(_p(t) for t in b) if run_b else none5
+    ck_f = ckpt[0] if (ckpt is not None and run_f) else None
+    ck_b = ckpt[1] if (ckpt is not None and run_b) else None
     with torch.cuda.device(dev):
         _lib.check(_lib.lib().wkv6_b200_bi_forward(_dtype_code(ref[0]), B, T, C, H,
-                                                   *fa, _p(s0_f), _p(y_f), _p(sT_f),
-                                                   *ba, _p(s0_b), _p(y_b), _p(sT_b), int(flags), _stream(ref[0])))
+                                                   *fa, _p(s0_f), _p(y_f), _p(sT_f), _p(ck_f),
+                                                   *ba, _p(s0_b), _p(y_b), _p(sT_b), _p(ck_b), int(flags),
+                                                   _stream(ref[0])))
     return y_f, y_b, sT_f, sT_b
 
 
 def bi_backward_raw(f, b, gy_f, gy_b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, gsT_f=None, gsT_b=None,
-                    want_gs0=False):
+                    want_gs0=False, ckpt=None):
     """Backward of bi_forward_raw: two launches (sweep A, sweep B) covering both directions.
     Returns two tuples (gr, gk, gv, gw, gu[B,C], gs0) -- None for a direction that did not run."""
     run_f, run_b = bool(flags & _lib.BI_L2R), bool(flags & _lib.BI_R2L)
@@ -129,7 +141,9 @@ def bi_backward_raw(f, b, gy_f, gy_b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None
 
     of, ob = outs(run_f), outs(run_b)
     L = _lib.lib()
-    ws_bytes = L.wkv6_b200_backward_workspace_bytes(_dtype_code(ref[0]), B, T, C, H, 2)
+    ws_bytes = 0 if ckpt is not None else L.wkv6_b200_backward_workspace_bytes(_dtype_code(ref[0]), B, T, C, H, 2)
+    ck_f = ckpt[0] if (ckpt is not None and run_f) else None
+    ck_b = ckpt[1] if (ckpt is not None and run_b) else None
     ws = torch.empty(ws_bytes, device=dev, dtype=torch.uint8) if ws_bytes else None
     none5 = (None,) * 5
     fa = tuple(_p(t) for t in f) if run_f else none5
@@ -137,8 +151,8 @@ def bi_backward_raw(f, b, gy_f, gy_b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None
     with torch.cuda.device(dev):
         _lib.check(L.wkv6_b200_bi_backward(
             _dtype_code(ref[0]), B, T, C, H,
-            *fa, _p(s0_f), _p(gy_f), _p(gsT_f), *[_p(t) for t in of],
-            *ba, _p(s0_b), _p(gy_b), _p(gsT_b), *[_p(t) for t in ob],
+            *fa, _p(s0_f), _p(gy_f), _p(gsT_f), _p(ck_f), *[_p(t) for t in of],
+            *ba, _p(s0_b), _p(gy_b), _p(gsT_b), _p(ck_b), *[_p(t) for t in ob],
             int(flags), _p(ws), ws_bytes, _stream(ref[0])))
     return of, ob
 

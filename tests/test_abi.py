@@ -25,21 +25,23 @@ def test_header_symbols_are_exported(built):
     L = built.lib()
     for s in declared:
         assert hasattr(L, s), s
-    assert L.wkv6_b200_abi_version() == 1
+    assert L.wkv6_b200_abi_version() == 2
 
 
 def test_argument_validation_without_gpu(built):
     L = built.lib()
     # C != H*64
-    rc = L.wkv6_b200_forward(0, 1, 4, 96, 1, None, None, None, None, None, None, None, None, 0, None)
+    rc = L.wkv6_b200_forward(0, 1, 4, 96, 1, None, None, None, None, None, None, None, None, None, 0, None)
     assert rc == -2 and b"64" in L.wkv6_b200_last_error()
-    rc = L.wkv6_b200_forward(7, 1, 4, 64, 1, None, None, None, None, None, None, None, None, 0, None)
+    rc = L.wkv6_b200_forward(7, 1, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None)
     assert rc == -3
     # empty batch is a no-op; NULL tensors with work to do are rejected before any launch
-    assert L.wkv6_b200_forward(0, 0, 4, 64, 1, None, None, None, None, None, None, None, None, 0, None) == 0
-    assert L.wkv6_b200_forward(0, 1, 4, 64, 1, None, None, None, None, None, None, None, None, 0, None) == -1
+    assert L.wkv6_b200_forward(0, 0, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None) == 0
+    assert L.wkv6_b200_forward(0, 1, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None) == -1
     assert L.wkv6_b200_backward_workspace_bytes(1, 2, 10, 128, 2, 2) == 2 * 2 * 2 * 64 * 4
-    assert L.wkv6_b200_backward_workspace_bytes(0, 2, 10, 128, 2, 2) == 2 * 2 * 2 * 64 * 4 + 2 * 2 * 10 * 128 * 2
+    assert L.wkv6_b200_backward_workspace_bytes(0, 2, 10, 128, 2, 2) == max(2 * 2 * 2 * 64 * 4 + 2 * 2 * 10 * 128 * 2,
+                                                                            2 * L.wkv6_b200_checkpoint_bytes(2, 10, 128, 2))
+    assert L.wkv6_b200_checkpoint_bytes(2, 130, 128, 2) == 2 * 2 * 3 * 64 * 64 * 2
 
 
 def test_torch_shim_registers_reference_schemas(built):
