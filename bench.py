@@ -26,13 +26,14 @@ CFG = dict(layers=12, C=512, H=8, B=16, T=750)
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="infer", choices=["infer", "train"])
     ap.add_argument("--algo", default="auto", choices=["auto", "scan", "chunk"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the fwd+bwd figures reported beside the inference line")
     return ap.parse_args()
 
 
@@ -71,22 +72,38 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_sample(threads=None):
-    """The oracle port timed on the host cores: ONE of the 12 blocks, both directions, full B x T."""
+_CPU_SETS = None
+
+
+def cpu_sample(passes=1, train=False):
+    """The oracle port (C restatement of the reference kernels, OpenMP over batch x head, all host cores) timed on
+    `passes` full passes of the workload: 12 blocks x both directions x full B x T, fp32.  Returns frames/s."""
+    global _CPU_SETS
     import torch
     import oracle
     from _torch_ref import make_inputs
-    if threads:
-        oracle.set_threads(threads)
     c = CFG
-    sets = [make_inputs(c["B"], c["T"], c["H"], 64, seed=s, dtype=torch.float32) for s in (11, 12)]
-    oracle.fwd(sets[0]["r"][:1], sets[0]["k"][:1], sets[0]["v"][:1], sets[0]["w"][:1], sets[0]["u"])   # warm
+    if _CPU_SETS is None:
+        _CPU_SETS = [make_inputs(c["B"], c["T"], c["H"], 64, seed=s, dtype=torch.float32, layer=s % 12) for s in (11, 12)]
+        s0 = _CPU_SETS[0]
+        oracle.fwd(s0["r"][:1], s0["k"][:1], s0["v"][:1], s0["w"][:1], s0["u"])   # warm (builds / loads the library)
     t0 = time.perf_counter()
-    for s, rev in zip(sets, (False, True)):
-        oracle.fwd(s["r"], s["k"], s["v"], s["w"], s["u"], rev=rev, prec="f32")
+    for _ in range(passes):
+        for layer in range(c["layers"]):
+            for s, rev in zip(_CPU_SETS, (False, True)):
+                oracle.fwd(s["r"], s["k"], s["v"], s["w"], s["u"], rev=rev, prec="f32")
+                if train:
+                    oracle.bwd(s["r"], s["k"], s["v"], s["w"], s["u"], s["gy"], rev=rev, prec="f32")
     dt = time.perf_counter() - t0
-    fps = c["B"] * c["T"] / (dt * c["layers"])
-    return fps, dt, oracle.num_threads()
+    return passes * c["B"] * c["T"] / dt, dt, oracle.num_threads()
+
+
+def cpu_baseline_bounded(budget_s=10.0, train=False):
+    """About `budget_s` seconds of CPU work: as many full passes as fit."""
+    fps1, dt1, th = cpu_sample(1, train)
+    n = max(1, min(200, int(budget_s / max(dt1, 1e-3))))
+    fps, dt, th = cpu_sample(n, train)
+    return fps, dt, th, n
 
 
 def config_dict(args, extra=None):
@@ -109,16 +126,21 @@ def run_reference(args):
         return
     import oracle
     oracle.build()
+    train = args.mode == "train"
+    steps = min(args.steps, 20)          # one step = one full pass on the CPU (~0.25 s fwd); bounded to a few minutes
+    warm = min(args.warmup, 2)
     vals = []
-    for i in range(args.warmup + args.steps):
-        fps, dt, th = cpu_sample()
-        if i >= args.warmup:
+    for i in range(warm + steps):
+        fps, dt, th = cpu_sample(1, train)
+        if i >= warm:
             vals.append((fps, dt))
-    fps = sum(v[0] for v in vals) / len(vals)
-    ms = 1e3 * sum(v[1] for v in vals) / len(vals) * CFG["layers"]
-    sample = "1 of 12 blocks, both directions, full B=16 x T=750, fp32 oracle port (OpenMP over batch x head); x12 extrapolated"
+    tot = sum(v[1] for v in vals)
+    fps = len(vals) * CFG["B"] * CFG["T"] / tot
+    ms = 1e3 * tot / len(vals)
+    sample = (f"{len(vals)} full passes (12 blocks x both directions x B=16 x T=750), fp32 oracle port of the reference "
+              "kernels, OpenMP over batch x head on all host cores (the reference itself has no CPU WKV6)")
     line = {"impl": "reference", "metric": "encoder frames/s (bi-WKV6)", "value": fps, "unit": "frames/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+            "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": config_dict(args),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": th, "kind": "port", "sample": sample},
@@ -165,93 +187,132 @@ def run_b200(args):
     L = _lib.lib()
     c = CFG
     B, T, C, H, NL = c["B"], c["T"], c["C"], c["H"], c["layers"]
-    train = args.mode == "train"
     dt = torch.bfloat16
-    layers = [make_layer_inputs(torch, dev, l, dt, train) for l in range(NL)]
+    layers = [make_layer_inputs(torch, dev, l, dt, True) for l in range(NL)]      # gy is only read by the backward
     mk = lambda: torch.empty(B, T, C, device=dev, dtype=dt)
     outs = [[mk(), mk()] for _ in range(NL)]
-    gouts = [[[mk() for _ in range(4)] + [torch.empty(B, C, device=dev, dtype=dt)] for _ in range(2)] for _ in range(NL)] if train else None
+    gouts = [[[mk() for _ in range(4)] + [torch.empty(B, C, device=dev, dtype=dt)] for _ in range(2)] for _ in range(NL)]
     stream = torch.cuda.current_stream().cuda_stream
     flags = _lib.BI_L2R | _lib.BI_R2L
     p = lambda t: t.data_ptr()
+    ck_bytes = L.wkv6_b200_checkpoint_bytes(B, T, C, H)
+    ckpts = [torch.empty((2, max(ck_bytes, 16)), device=dev, dtype=torch.uint8) for _ in range(NL)]
+    ws_bytes = L.wkv6_b200_backward_workspace_bytes(0, B, T, C, H, 2)
+    ws = torch.empty(max(ws_bytes, 16), device=dev, dtype=torch.uint8)
 
-    ck_bytes = L.wkv6_b200_checkpoint_bytes(B, T, C, H) if train else 0
-    ckpts = [torch.empty((2, ck_bytes), device=dev, dtype=torch.uint8) for _ in range(NL)] if train else None
-    ck = lambda l, d: (ckpts[l][d].data_ptr() if train else None)
-
-    def fwd_layer(l, ins=None, ys=None):
+    def fwd_layer(l, train, ins=None, ys=None):
         f, b = ins or layers[l]
         yf, yb = ys or outs[l]
-        _lib.check(L.wkv6_b200_bi_forward(0, B, T, C, H, p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(yf), None, ck(l, 0),
-                                          p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(yb), None, ck(l, 1), flags, stream))
-
-    ws_bytes = L.wkv6_b200_backward_workspace_bytes(0, B, T, C, H, 2) if train else 0
-    ws = torch.empty(max(ws_bytes, 16), device=dev, dtype=torch.uint8)
+        ckf = p(ckpts[l][0]) if train else None
+        ckb = p(ckpts[l][1]) if train else None
+        _lib.check(L.wkv6_b200_bi_forward(0, B, T, C, H, p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(yf), None, ckf,
+                                          p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(yb), None, ckb, flags, stream))
 
     def bwd_layer(l):
         f, b = layers[l]
         gf, gb = gouts[l]
         _lib.check(L.wkv6_b200_bi_backward(
             0, B, T, C, H,
-            p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(f[5]), None, ck(l, 0), *[p(x) for x in gf], None,
-            p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(b[5]), None, ck(l, 1), *[p(x) for x in gb], None,
+            p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(f[5]), None, p(ckpts[l][0]), *[p(x) for x in gf], None,
+            p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(b[5]), None, p(ckpts[l][1]), *[p(x) for x in gb], None,
             flags, p(ws), ws_bytes, stream))
-
-    ev_pairs = []
-
-    def step(record=False):
-        for l in range(NL):
-            if record:
-                e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-                e0.record()
-            fwd_layer(l)
-            if record:
-                e1.record(); ev_pairs.append((e0, e1))
-        if train:
-            for l in reversed(range(NL)):
-                bwd_layer(l)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    n0 = pk.launch_count()
-    sampler = ClockSampler(local); sampler.start()
-    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
-    t0.record()
-    for _ in range(args.steps):
-        step(record=True)
-    t1.record()
-    barrier()
-    sampler.stop_flag = True
-    launches = pk.launch_count() - n0
-    ms_total = t0.elapsed_time(t1)
-    tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_total = float(tt.item())
-    ms_step = ms_total / args.steps
-    value = world * B * T / (ms_step * 1e-3)
-    kern_ms = sum(a.elapsed_time(b) for a, b in ev_pairs) / len(ev_pairs)
-    alg_bytes = 2 * 5 * B * T * C * 2                     # both directions: read r,k,v,w + write y, bf16
-    pk_, how = peaks()
-    achieved = alg_bytes / (kern_ms * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": "wkv6 bidirectional forward (one launch per block)", "achieved": achieved,
-            "peak": pk_["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk_["hbm_gbs"], "peak_source": how,
-            "traffic": None, "alg_bytes_per_launch": alg_bytes, "kernel_ms": kern_ms}
+    def allmax(ms):
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
-    # ---- end to end: pinned host inputs -> H2D -> op -> D2H of y, every step, through the public API
+    def timed(train, steps, warmup, sampler=None):
+        """`steps` steps of the 12-block workload (fwd, or fwd then bwd in reverse block order); per-kernel events on
+        the launching stream for the roofline figures.  Returns ms/step (max over ranks), avg fwd-launch ms, avg
+        bwd-launch ms, launches."""
+        fev, bev = [], []
+
+        def step(record):
+            for l in range(NL):
+                if record:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                fwd_layer(l, train)
+                if record:
+                    e1.record(); fev.append((e0, e1))
+            if train:
+                for l in reversed(range(NL)):
+                    if record:
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record()
+                    bwd_layer(l)
+                    if record:
+                        e1.record(); bev.append((e0, e1))
+
+        for _ in range(warmup):
+            step(False)
+        barrier()
+        n0 = pk.launch_count()
+        if sampler:
+            sampler.start()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(steps):
+            step(True)
+        t1.record()
+        barrier()
+        launches = pk.launch_count() - n0
+        ms = allmax(t0.elapsed_time(t1)) / steps
+        fk = sum(a.elapsed_time(b) for a, b in fev) / len(fev)
+        bk = sum(a.elapsed_time(b) for a, b in bev) / len(bev) if bev else None
+        return ms, fk, bk, launches
+
+    train = args.mode == "train"
+    sampler = ClockSampler(local)
+    ms_step, fwd_ms, bwd_ms, launches = timed(train, args.steps, args.warmup, sampler)
+    if len(sampler.rows) < 3:            # a short timed region: keep the same load running until the sampler has seen it
+        t_end = time.time() + 1.0
+        while time.time() < t_end and len(sampler.rows) < 4:
+            for l in range(NL):
+                fwd_layer(l, train)
+            torch.cuda.synchronize()
+    sampler.stop_flag = True
+    value = world * B * T / (ms_step * 1e-3)
+    pk_, how = peaks()
+    fwd_bytes = 2 * 5 * B * T * C * 2                     # both directions: read r,k,v,w + write y, bf16
+    bwd_bytes = 2 * 9 * B * T * C * 2                     # read r,k,v,w,gy + write gr,gk,gv,gw
+
+    def roof(kernel, nbytes, ms):
+        ach = nbytes / (ms * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": kernel, "achieved": ach, "peak": pk_["hbm_gbs"], "unit": "GB/s",
+                "frac": ach / pk_["hbm_gbs"], "peak_source": how, "traffic": None, "alg_bytes_per_launch": nbytes,
+                "kernel_ms": ms}
+
+    roofline = roof("wkv6_fwd_chunk_kernel: bidirectional forward, one launch per block", fwd_bytes, fwd_ms)
+    extra = {}
+    if train:
+        roofline = roof("wkv6_bwd_chunk_kernel: bidirectional backward, one launch per block", bwd_bytes, bwd_ms)
+        extra["roofline_fwd"] = roof("wkv6_fwd_chunk_kernel (+ checkpoint stores)", fwd_bytes, fwd_ms)
+        extra["roofline_fwd_bwd"] = roof("forward + backward launches of one block", fwd_bytes + bwd_bytes, fwd_ms + bwd_ms)
+    elif not args.no_train:
+        # the same workload as a training step (fwd + bwd), reported beside the inference headline
+        tsteps = max(3, min(args.steps, 30))
+        tms, tf, tb, _ = timed(True, tsteps, 3)
+        extra["train"] = {"metric": "encoder frames/s (bi-WKV6 fwd+bwd)", "value": world * B * T / (tms * 1e-3),
+                          "unit": "frames/s", "ms_per_step": tms, "steps": tsteps,
+                          "roofline_bwd": roof("wkv6_bwd_chunk_kernel", bwd_bytes, tb),
+                          "roofline_fwd_bwd": roof("forward + backward launches of one block", fwd_bytes + bwd_bytes, tf + tb)}
+
+    # ---- end to end: pinned host inputs -> H2D -> op -> D2H of y, every step, through the C ABI
     e2e = None
     if not args.no_e2e and not train:
         host = [make_layer_inputs(torch, dev, l, dt, False, pinned=True) for l in range(2)]   # 2 distinct blocks, reused
-        stage = [[[torch.empty_like(x, device=dev) for x in s] for s in host[0]] for _ in range(2)]
+        stage = [[[torch.empty_like(x, device=dev) for x in s_] for s_ in host[0]] for _ in range(2)]
         ystage = [[mk(), mk()] for _ in range(2)]
         yhost = [[torch.empty(B, T, C, dtype=dt).pin_memory() for _ in range(2)] for _ in range(2)]
-        h2d = sum(x.numel() * x.element_size() for s in host[0] for x in s) * NL
+        h2d = sum(x.numel() * x.element_size() for s_ in host[0] for x in s_) * NL
         d2h = 2 * B * T * C * 2 * NL
 
         def e2e_step():
@@ -260,7 +321,7 @@ def run_b200(args):
                 for s_h, s_d in zip(src, dst):
                     for xh, xd in zip(s_h, s_d):
                         xd.copy_(xh, non_blocking=True)
-                fwd_layer(l, ins=dst, ys=ystage[l & 1])
+                fwd_layer(l, False, ins=dst, ys=ystage[l & 1])
                 for yh, yd in zip(yhost[l & 1], ystage[l & 1]):
                     yh.copy_(yd, non_blocking=True)
 
@@ -271,23 +332,23 @@ def run_b200(args):
         for _ in range(e2e_steps):
             e2e_step()
         b_.record(); barrier()
-        te = torch.tensor([a.elapsed_time(b_)], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * B * T / (float(te.item()) / e2e_steps * 1e-3), "unit": "frames/s",
+        te = allmax(a.elapsed_time(b_))
+        e2e = {"value": world * B * T / (te / e2e_steps * 1e-3), "unit": "frames/s",
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps}
 
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            fps, secs, th = cpu_sample()
+            fps, secs, th, n = cpu_baseline_bounded(10.0, train)
             cpu = {"value": fps, "unit": "frames/s", "cores": th, "kind": "port",
-                   "sample": f"1 of 12 blocks, both directions, full B=16 x T=750 ({secs:.2f} s of CPU work), x12 extrapolated"}
-        line = {"metric": "encoder frames/s (bi-WKV6)", "value": value, "unit": "frames/s", "n_gpus": world,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+                   "sample": f"{n} full passes of the workload (12 blocks x both directions x B=16 x T=750, fp32"
+                             f"{', fwd+bwd' if train else ', fwd'}): {secs:.1f} s of CPU work on {th} threads"}
+        line = {"metric": "encoder frames/s (bi-WKV6%s)" % (" fwd+bwd" if train else ""), "value": value, "unit": "frames/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                "config": config_dict(args, {"algo": args.algo}), "roofline": roof, "cpu_baseline": cpu, "e2e": e2e,
+                "config": config_dict(args, {"algo": args.algo}), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": launches, "clocks": sampler.summary()}
+        line.update(extra)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
