@@ -40,7 +40,9 @@ struct ChunkSmem {
 
 __global__ void __launch_bounds__(128, 2) wkv6_fwd_chunk_kernel(const __grid_constant__ Params p) {
     extern __shared__ __align__(1024) uint8_t smem_bytes[];
-    ChunkSmem& sm = *reinterpret_cast<ChunkSmem*>((reinterpret_cast<uintptr_t>(smem_bytes) + 1023) & ~uintptr_t(1023));
+    // offset arithmetic on the __shared__ array (not a uintptr_t round trip) keeps the address space visible to the
+    // compiler: LDS/STS instead of generic LD/ST
+    ChunkSmem& sm = *reinterpret_cast<ChunkSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int BH = p.B * p.H;

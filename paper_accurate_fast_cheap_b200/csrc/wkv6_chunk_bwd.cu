@@ -48,6 +48,10 @@ __device__ __forceinline__ void ld4bf(const uint8_t* p, float (&f)[4]) {   // 4 
     f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
     f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
 }
+__device__ __forceinline__ void up4bf(const uint2 q, float (&f)[4]) {
+    f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
+    f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
+}
 __device__ __forceinline__ void st4bf(uint8_t* p, const float (&f)[4]) {
     *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]));
 }
@@ -86,7 +90,7 @@ struct BwdChunkSmem {
     float bonus[2][CL];                      // sum_j r u k per row (two channel halves)
     float vg[CL];                            // v_p . gy_p per row
     float gured[8][N / 2];
-    alignas(8) uint64_t bar_in, bar_m1, bar_m2;
+    alignas(8) uint64_t bar_rkw, bar_vg, bar_sp, bar_m1, bar_mp, bar_m2;
     uint32_t tmem_base;
 };
 static_assert(sizeof(BwdChunkSmem) <= 226 * 1024, "shared memory budget");
@@ -94,7 +98,9 @@ static_assert(CL * XSTR * 4 <= 20 * 1024, "xk must fit into the rp region");
 
 __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_constant__ Params p) {
     extern __shared__ __align__(1024) uint8_t smem_bytes[];
-    BwdChunkSmem& sm = *reinterpret_cast<BwdChunkSmem*>((reinterpret_cast<uintptr_t>(smem_bytes) + 1023) & ~uintptr_t(1023));
+    // offset arithmetic on the __shared__ array (not a uintptr_t round trip) keeps the address space visible to the
+    // compiler: LDS/STS instead of generic LD/ST
+    BwdChunkSmem& sm = *reinterpret_cast<BwdChunkSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int BH = p.B * p.H;
@@ -117,7 +123,10 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     uint8_t* const o_gv = sm.pt;
 
     if (tid == 0) {
-        mbar_init(&sm.bar_in, 1);
+        mbar_init(&sm.bar_rkw, 1);
+        mbar_init(&sm.bar_vg, 1);
+        mbar_init(&sm.bar_sp, 1);
+        mbar_init(&sm.bar_mp, 1);
         mbar_init(&sm.bar_m1, 1);
         mbar_init(&sm.bar_m2, 1);
         fence_barrier_init();
@@ -172,6 +181,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
     };
     store_cp();
+    fence_proxy_async();
 
     tc_fence_before();
     __syncthreads();
@@ -180,18 +190,27 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     const uint32_t tQ = tbase, tP = tbase + 64, tRS = tbase + 128, tKC = tbase + 192, tR = tbase + 256, tK = tbase + 320,
                    tGV = tbase + 384, tDC = tbase + 448;
 
-    auto issue_tma = [&](int cb) {   // thread 0 only
-        const int c = nchunks - 1 - cb;
-        const int q = rev ? nchunks - 1 - c : c;
-        mbar_arrive_expect_tx(&sm.bar_in, 6u * CL * 128);
-        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_in, h * N, q * CL, b);
-        tma_load_3d(sm.raw_k, &D.mk, &sm.bar_in, h * N, q * CL, b);
-        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_in, h * N, q * CL, b);
-        tma_load_3d(sm.v, &D.mv, &sm.bar_in, h * N, q * CL, b);
-        tma_load_3d(sm.g, &D.mg, &sm.bar_in, h * N, q * CL, b);
-        tma_load_2d(sm.sp, &D.mc, &sm.bar_in, 0, (bh * nchunks + c) * N);
+    // Loads of the next chunk are issued as soon as their landing tiles are dead: r/k/w after the operand tiles are
+    // built (r, k live on in registers), v/gy after the phase-2 MMAs, the checkpoint after the anchor sum.
+    auto tile_q = [&](int cb) { const int c = nchunks - 1 - cb; return rev ? nchunks - 1 - c : c; };
+    auto issue_rkw = [&](int cb) {   // thread 0 only
+        const int q = tile_q(cb);
+        mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
+        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q * CL, b);
+        tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q * CL, b);
+        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q * CL, b);
     };
-    if (tid == 0 && nchunks > 0) issue_tma(0);
+    auto issue_vg = [&](int cb) {
+        const int q = tile_q(cb);
+        mbar_arrive_expect_tx(&sm.bar_vg, 2u * CL * 128);
+        tma_load_3d(sm.v, &D.mv, &sm.bar_vg, h * N, q * CL, b);
+        tma_load_3d(sm.g, &D.mg, &sm.bar_vg, h * N, q * CL, b);
+    };
+    auto issue_sp = [&](int cb) {
+        mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
+        tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1 - cb)) * N);
+    };
+    if (tid == 0 && nchunks > 0) { issue_rkw(0); issue_vg(0); issue_sp(0); }
 
     constexpr uint32_t ID_KK64 = umma_idesc(0, 0, 64, 64);
     constexpr uint32_t ID_KK16 = umma_idesc(0, 0, 64, 16);
@@ -204,11 +223,26 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         const int q = rev ? nchunks - 1 - c : c;         // tile index in memory
         const int t0 = q * CL;
         const uint32_t par = cb & 1;
-        if (tid == 0) tma_store_wait_read<0>();          // staging tiles of the previous chunk have been read
+        if (tid == 0) {
+            tma_store_wait_read<0>();                    // staging tiles of the previous chunk have been read
+            // ---- MMA phase 1a: everything that needs no preprocessing (V, G, S_0, C are raw / carried tiles)
+            mbar_wait(&sm.bar_vg, par);
+            mbar_wait(&sm.bar_sp, par);
+            tc_fence_after();
+            const uint32_t a_g = smem_u32(sm.g), a_v = smem_u32(sm.v), a_sp = smem_u32(sm.sp), a_cp = smem_u32(sm.cp);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tQ, desc_k(a_g + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tRS, desc_k(a_sp + ks * 32), desc_k(a_g + ks * 32), ID_KK64, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tKC, desc_k(a_cp + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
+            umma_commit(&sm.bar_m1);
+        }
 
         // ================= phase 1: decays, in-block cumulative sums, Rtil, Ktil(own), bonus
-        mbar_wait(&sm.bar_in, par);
+        mbar_wait(&sm.bar_rkw, par);
         float eo[4][4], ei[4][4], ew[4][4], bt[4];
+        uint2 rpk[4], kpk[4];                            // this thread's r and k (bf16 x4 per row) for the later phases
         int rows[4];
         {
             float rr[4][4], kk[4][4], l2[4][4], bsum[4];
@@ -219,8 +253,10 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 rows[r] = row;
                 const int off = sw_chunk(row, cchunk) + coff;
                 float w4[4];
-                ld4bf(sm.raw_r + off, rr[r]);
-                ld4bf(sm.raw_k + off, kk[r]);
+                rpk[r] = *reinterpret_cast<const uint2*>(sm.raw_r + off);
+                kpk[r] = *reinterpret_cast<const uint2*>(sm.raw_k + off);
+                up4bf(rpk[r], rr[r]);
+                up4bf(kpk[r], kk[r]);
                 ld4bf(sm.raw_w + off, w4);
                 const bool valid = t0 + row < T;
                 float bs = 0.f;
@@ -313,18 +349,12 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 }
             }
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
+            for (int r = 0; r < 4; r++) {       // K side: needed by the P^T MMAs
                 const int off = sw_chunk(rows[r], cchunk) + coff;
-                float ro[4], ko[4], x4[4];
-                ld4bf(sm.raw_r + off, ro);
-                ld4bf(sm.raw_k + off, ko);
+                float ko[4], x4[4];
+                up4bf(kpk[r], ko);
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    ro[e] *= eo[r][e];
-                    ko[e] *= ei[r][e];
-                    x4[e] = ro[e] * fst[e];
-                }
-                st4bf_hilo(sm.rst + off, sm.rst_lo + off, x4);
+                for (int e = 0; e < 4; e++) ko[e] *= ei[r][e];
 #pragma unroll
                 for (int m = 0; m < 4; m++) {
                     if (m >= I) {               // target variant I' = m + 1 (I' = 4 -> Kend)
@@ -334,6 +364,36 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                         else st4bf_hilo(sm.kt + vbK[m + 1] + off, sm.kt_lo + vbK[m + 1] + off, x4);
                     }
                 }
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            __syncthreads();   // B2: Rtil, Ktil variants complete; raw r / k / w tiles are dead
+
+            // ================= MMA phase 1b: P^T (runs under the R-side preprocessing below)
+            if (tid == 0) {
+                tc_fence_after();
+                const uint32_t a_kt = smem_u32(sm.kt), a_roff = smem_u32(sm.roff);
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int rowlo = rev ? 48 - 16 * i : 16 * i;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++)
+                        umma(tP + rowlo, desc_k(a_kt + vbK[i] + ks * 32), desc_k(a_roff + rowlo * 128 + ks * 32), ID_KK16, ks > 0);
+                }
+                umma_commit(&sm.bar_mp);
+                if (cb + 1 < nchunks) issue_rkw(cb + 1);
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++) {       // R side: needed by the phase-2 MMAs only
+                const int off = sw_chunk(rows[r], cchunk) + coff;
+                float ro[4], x4[4];
+                up4bf(rpk[r], ro);
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    ro[e] *= eo[r][e];
+                    x4[e] = ro[e] * fst[e];
+                }
+                st4bf_hilo(sm.rst + off, sm.rst_lo + off, x4);
 #pragma unroll
                 for (int J = 0; J < 4; J++) {
                     if (J <= I) {
@@ -343,30 +403,6 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     }
                 }
             }
-        }
-        fence_proxy_async();
-        tc_fence_before();
-        __syncthreads();   // B2: operand tiles complete
-
-        // ================= MMA phase 1
-        if (tid == 0) {
-            tc_fence_after();
-            const uint32_t a_g = smem_u32(sm.g), a_v = smem_u32(sm.v), a_kt = smem_u32(sm.kt), a_roff = smem_u32(sm.roff),
-                           a_sp = smem_u32(sm.sp), a_cp = smem_u32(sm.cp);
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tQ, desc_k(a_g + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const int rowlo = rev ? 48 - 16 * i : 16 * i;
-#pragma unroll
-                for (int ks = 0; ks < 4; ks++)
-                    umma(tP + rowlo, desc_k(a_kt + vbK[i] + ks * 32), desc_k(a_roff + rowlo * 128 + ks * 32), ID_KK16, ks > 0);
-            }
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tRS, desc_k(a_sp + ks * 32), desc_k(a_g + ks * 32), ID_KK64, ks > 0);
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tKC, desc_k(a_cp + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
-            umma_commit(&sm.bar_m1);
         }
 
         // ================= E1: Q -> masked Q, Q^T, vg;  P^T -> masked P^T with the bonus diagonal
@@ -393,6 +429,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     const int qc = fcol + 8 * rep;
                     *reinterpret_cast<uint32_t*>(sm.qm + sw_chunk(pp, qc >> 3) + (qc & 7) * 2) = pack_bf16(y[0], y[1]);
                 }
+            mbar_wait(&sm.bar_mp, par);
+            tc_fence_after();
             tmem_ld_16x32(tP + lane_field + 32 * half, x);
 #pragma unroll
             for (int rep = 0; rep < 4; rep++)
@@ -455,6 +493,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         // ================= E2: drain the phase-2 accumulators
         mbar_wait(&sm.bar_m2, par);
         tc_fence_after();
+        if (tid == 0 && cb + 1 < nchunks) issue_vg(cb + 1);   // V, G are dead once the phase-2 MMAs have completed
         {
             // per-thread decay factors of its two rows j (log2 sums of the sub-block totals)
             float t0j[4], t1j[4];
@@ -544,6 +583,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             store_cp();
         }
         __syncthreads();   // B4: xr / xk / hst / vg visible; all TMEM reads of this chunk done
+        if (tid == 0 && cb + 1 < nchunks) issue_sp(cb + 1);   // S_0 tile is dead after the anchor sum
 
         // ================= final epilogue (row-major): gr, gk, gu, gw
         {
@@ -559,8 +599,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 const int row = rows[r];
                 const int off = sw_chunk(row, cchunk) + coff;
                 float rr[4], kk[4], gr4[4], gk4[4];
-                ld4bf(sm.raw_r + off, rr);
-                ld4bf(sm.raw_k + off, kk);
+                up4bf(rpk[r], rr);
+                up4bf(kpk[r], kk);
                 const float vg = sm.vg[row];
                 const float4 a4 = *reinterpret_cast<const float4*>(&xr[row * XSTR + c0]);
                 const float4 b4 = *reinterpret_cast<const float4*>(&xk[row * XSTR + c0]);
@@ -633,7 +673,6 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             tma_store_3d(&D.mgv, o_gv, h * N, t0, b);
             tma_store_3d(&D.mgw, sm.o_gw, h * N, t0, b);
             tma_store_commit();
-            if (cb + 1 < nchunks) issue_tma(cb + 1);
         }
     }
 
