@@ -65,6 +65,8 @@ int  wkv6_b200_abi_version(void);
 const char* wkv6_b200_last_error(void);
 /* Number of kernels this library has launched since load (the bench's gpu_launches). */
 long long wkv6_b200_launch_count(void);
+/* Debug aid: clock64() trace of one CTA of the chunk kernels (see csrc/wkv6_capi.cu); not part of the data path. */
+int  wkv6_b200_debug_trace(int enable, unsigned long long* out);
 void wkv6_b200_set_algo(int algo);
 int  wkv6_b200_get_algo(void);
 

@@ -17,6 +17,9 @@ static std::atomic<int> g_algo{WKV6_ALGO_AUTO};
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+static unsigned long long* g_dbg = nullptr;
+unsigned long long* debug_trace_buffer() { return g_dbg; }
+
 static int fail(int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -279,6 +282,17 @@ using namespace wkv6;
 extern "C" {
 
 int wkv6_b200_abi_version(void) { return 2; }
+/* Debug: enable != 0 allocates a 128-slot device buffer that CTA 0 of the chunk kernels fills with clock64() stamps
+ * (forward: slots 0..31, backward: 64..95); `out` (host, 128 entries) receives the current contents. */
+int wkv6_b200_debug_trace(int enable, unsigned long long* out) {
+    if (enable && !g_dbg) {
+        if (cudaMalloc(&g_dbg, 128 * sizeof(unsigned long long)) != cudaSuccess) return -1;
+        cudaMemset(g_dbg, 0, 128 * sizeof(unsigned long long));
+    }
+    if (out && g_dbg) cudaMemcpy(out, g_dbg, 128 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    if (!enable && g_dbg) { cudaFree(g_dbg); g_dbg = nullptr; }
+    return 0;
+}
 size_t wkv6_b200_checkpoint_bytes(int B, int T, int C, int H) {
     (void)C;
     return (B <= 0 || T <= 0 || H <= 0) ? 0 : ckpt_bytes(B, T, H);

@@ -31,40 +31,6 @@ namespace wkv6 {
 
 constexpr int XSTR = 68;   // row stride (floats) of the fp32 transposition buffers: conflict-free scalar stores
 
-__device__ __forceinline__ void tmem_ld_16x32(uint32_t taddr, float (&v)[16]) {   // 16 lanes x 32 columns
-    uint32_t u[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]), "=r"(u[9]),
-          "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; i++) v[i] = __uint_as_float(u[i]);
-}
-
-__device__ __forceinline__ void ld4bf(const uint8_t* p, float (&f)[4]) {   // 4 consecutive bf16 -> fp32
-    const uint2 q = *reinterpret_cast<const uint2*>(p);
-    f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
-    f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
-}
-__device__ __forceinline__ void up4bf(const uint2 q, float (&f)[4]) {
-    f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
-    f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
-}
-__device__ __forceinline__ void st4bf(uint8_t* p, const float (&f)[4]) {
-    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]));
-}
-// x = hi + lo with hi = bf16(x), lo = bf16(x - hi): two bf16 tiles carry ~16 mantissa bits through the MMA.  Needed
-// where two differently factorised sums must cancel (the gw prefix sum), see DESIGN.md.
-__device__ __forceinline__ void st4bf_hilo(uint8_t* hi, uint8_t* lo, const float (&f)[4]) {
-    const uint32_t h0 = pack_bf16(f[0], f[1]), h1 = pack_bf16(f[2], f[3]);
-    *reinterpret_cast<uint2*>(hi) = make_uint2(h0, h1);
-    const float l0 = f[0] - __uint_as_float(h0 << 16), l1 = f[1] - __uint_as_float(h0 & 0xffff0000u);
-    const float l2 = f[2] - __uint_as_float(h1 << 16), l3 = f[3] - __uint_as_float(h1 & 0xffff0000u);
-    *reinterpret_cast<uint2*>(lo) = make_uint2(pack_bf16(l0, l1), pack_bf16(l2, l3));
-}
-
 struct BwdChunkSmem {
     alignas(1024) uint8_t raw_r[CL * 128];   // TMA landing tiles (bf16, 128B swizzle), rows = time, cols = channel
     alignas(1024) uint8_t raw_k[CL * 128];
@@ -126,9 +92,9 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         mbar_init(&sm.bar_rkw, 1);
         mbar_init(&sm.bar_vg, 1);
         mbar_init(&sm.bar_sp, 1);
-        mbar_init(&sm.bar_mp, 1);
-        mbar_init(&sm.bar_m1, 1);
-        mbar_init(&sm.bar_m2, 1);
+        mbar_init(&sm.bar_mp, 4);     // MMA groups are issued by several warps' lane 0 in parallel (an issue costs
+        mbar_init(&sm.bar_m1, 3);     // ~50 cycles of dependent uniform-datapath work); every issuer commits
+        mbar_init(&sm.bar_m2, 6);
         fence_barrier_init();
         tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
         tma_prefetch_desc(&D.mg); tma_prefetch_desc(&D.mc);
@@ -190,6 +156,17 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     const uint32_t tQ = tbase, tP = tbase + 64, tRS = tbase + 128, tKC = tbase + 192, tR = tbase + 256, tK = tbase + 320,
                    tGV = tbase + 384, tDC = tbase + 448;
 
+    // UMMA smem descriptors of every operand tile, built once: inside the chunk loop a descriptor is base + (byte
+    // offset >> 4), one 64-bit add on the uniform datapath instead of a dozen dependent uniform ops per MMA.
+    const uint64_t dk_g = desc_k(smem_u32(sm.g)), dk_v = desc_k(smem_u32(sm.v)), dk_sp = desc_k(smem_u32(sm.sp)),
+                   dk_cp = desc_k(smem_u32(sm.cp)), dk_kt = desc_k(smem_u32(sm.kt)), dk_roff = desc_k(smem_u32(sm.roff)),
+                   dk_qm = desc_k(smem_u32(sm.qm)), dk_qmt = desc_k(smem_u32(sm.qmt)), dk_pt = desc_k(smem_u32(sm.pt)),
+                   dk_kend = desc_k(smem_u32(kend));
+    const uint64_t dm_kt = desc_mn(smem_u32(sm.kt)), dm_ktl = desc_mn(smem_u32(sm.kt_lo)), dm_rp = desc_mn(smem_u32(sm.rp)),
+                   dm_rpl = desc_mn(smem_u32(sm.rp_lo)), dm_g = desc_mn(smem_u32(sm.g)), dm_cp = desc_mn(smem_u32(sm.cp)),
+                   dm_rst = desc_mn(smem_u32(sm.rst)), dm_rstl = desc_mn(smem_u32(sm.rst_lo));
+#define DOFF(bytes) ((uint64_t)((bytes) >> 4))
+
     // Loads of the next chunk are issued as soon as their landing tiles are dead: r/k/w after the operand tiles are
     // built (r, k live on in registers), v/gy after the phase-2 MMAs, the checkpoint after the anchor sum.
     auto tile_q = [&](int cb) { const int c = nchunks - 1 - cb; return rev ? nchunks - 1 - c : c; };
@@ -223,24 +200,31 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         const int q = rev ? nchunks - 1 - c : c;         // tile index in memory
         const int t0 = q * CL;
         const uint32_t par = cb & 1;
-        if (tid == 0) {
-            tma_store_wait_read<0>();                    // staging tiles of the previous chunk have been read
+        const int c_ts = cb;
+        WKV6_TS(64, 0);
+        if (tid == 0) tma_store_wait_read<0>();          // staging tiles of the previous chunk have been read
+        if (lane == 0 && warp < 3) {
             // ---- MMA phase 1a: everything that needs no preprocessing (V, G, S_0, C are raw / carried tiles)
             mbar_wait(&sm.bar_vg, par);
             mbar_wait(&sm.bar_sp, par);
             tc_fence_after();
-            const uint32_t a_g = smem_u32(sm.g), a_v = smem_u32(sm.v), a_sp = smem_u32(sm.sp), a_cp = smem_u32(sm.cp);
+            if (warp == 0) {
 #pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tQ, desc_k(a_g + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
+                for (int ks = 0; ks < 4; ks++) umma(tQ, dk_g + DOFF(ks * 32), dk_v + DOFF(ks * 32), ID_KK64, ks > 0);
+            } else if (warp == 1) {
 #pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tRS, desc_k(a_sp + ks * 32), desc_k(a_g + ks * 32), ID_KK64, ks > 0);
+                for (int ks = 0; ks < 4; ks++) umma(tRS, dk_sp + DOFF(ks * 32), dk_g + DOFF(ks * 32), ID_KK64, ks > 0);
+            } else {
 #pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tKC, desc_k(a_cp + ks * 32), desc_k(a_v + ks * 32), ID_KK64, ks > 0);
+                for (int ks = 0; ks < 4; ks++) umma(tKC, dk_cp + DOFF(ks * 32), dk_v + DOFF(ks * 32), ID_KK64, ks > 0);
+            }
             umma_commit(&sm.bar_m1);
         }
+        __syncwarp();
 
         // ================= phase 1: decays, in-block cumulative sums, Rtil, Ktil(own), bonus
         mbar_wait(&sm.bar_rkw, par);
+        WKV6_TS(64, 1);
         float eo[4][4], ei[4][4], ew[4][4], bt[4];
         uint2 rpk[4], kpk[4];                            // this thread's r and k (bf16 x4 per row) for the later phases
         int rows[4];
@@ -309,6 +293,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 if (cq == 0) sm.bonus[ch][rows[r]] = bs;
             }
         }
+        WKV6_TS(64, 2);
         __syncthreads();   // B1: blocktot / bonus visible
 
         // ================= phase 1b: cross-block factors -> Rst, Ktil(I' > I), Kend, Rtil'(J <= I)
@@ -367,22 +352,23 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
             fence_proxy_async();
             tc_fence_before();
+            WKV6_TS(64, 3);
             __syncthreads();   // B2: Rtil, Ktil variants complete; raw r / k / w tiles are dead
+            WKV6_TS(64, 4);
 
             // ================= MMA phase 1b: P^T (runs under the R-side preprocessing below)
-            if (tid == 0) {
+            if (lane == 0 && warp < 4) {
                 tc_fence_after();
-                const uint32_t a_kt = smem_u32(sm.kt), a_roff = smem_u32(sm.roff);
+                const int i = warp;
+                const int rowlo = rev ? 48 - 16 * i : 16 * i;
+                const int vbi = i == 0 ? vbK[0] : i == 1 ? vbK[1] : i == 2 ? vbK[2] : vbK[3];
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int rowlo = rev ? 48 - 16 * i : 16 * i;
-#pragma unroll
-                    for (int ks = 0; ks < 4; ks++)
-                        umma(tP + rowlo, desc_k(a_kt + vbK[i] + ks * 32), desc_k(a_roff + rowlo * 128 + ks * 32), ID_KK16, ks > 0);
-                }
+                for (int ks = 0; ks < 4; ks++)
+                    umma(tP + rowlo, dk_kt + DOFF(vbi + ks * 32), dk_roff + DOFF(rowlo * 128 + ks * 32), ID_KK16, ks > 0);
                 umma_commit(&sm.bar_mp);
-                if (cb + 1 < nchunks) issue_rkw(cb + 1);
+                if (tid == 0 && cb + 1 < nchunks) issue_rkw(cb + 1);
             }
+            __syncwarp();
 #pragma unroll
             for (int r = 0; r < 4; r++) {       // R side: needed by the phase-2 MMAs only
                 const int off = sw_chunk(rows[r], cchunk) + coff;
@@ -405,8 +391,10 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
         }
 
+        WKV6_TS(64, 5);
         // ================= E1: Q -> masked Q, Q^T, vg;  P^T -> masked P^T with the bonus diagonal
         mbar_wait(&sm.bar_m1, par);
+        WKV6_TS(64, 6);
         tc_fence_after();
         {
             float x[16];
@@ -430,6 +418,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     *reinterpret_cast<uint32_t*>(sm.qm + sw_chunk(pp, qc >> 3) + (qc & 7) * 2) = pack_bf16(y[0], y[1]);
                 }
             mbar_wait(&sm.bar_mp, par);
+            WKV6_TS(64, 7);
             tc_fence_after();
             tmem_ld_16x32(tP + lane_field + 32 * half, x);
 #pragma unroll
@@ -450,48 +439,53 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         }
         fence_proxy_async();
         tc_fence_before();
+        WKV6_TS(64, 8);
         __syncthreads();   // B3: masked tiles complete
+        WKV6_TS(64, 9);
 
-        // ================= MMA phase 2
-        if (tid == 0) {
+        // ================= MMA phase 2: six issuing lanes (warps 0-3: R^T and K^T group w; warp 4: GV; warp 5: dC)
+        if (lane == 0 && warp < 6) {
             tc_fence_after();
-            const uint32_t a_g = smem_u32(sm.g), a_kt = smem_u32(sm.kt), a_rp = smem_u32(sm.rp), a_qm = smem_u32(sm.qm),
-                           a_qmt = smem_u32(sm.qmt), a_pt = smem_u32(sm.pt), a_kend = smem_u32(kend), a_cp = smem_u32(sm.cp),
-                           a_rst = smem_u32(sm.rst), a_rstl = smem_u32(sm.rst_lo), a_ktl = smem_u32(sm.kt_lo),
-                           a_rpl = smem_u32(sm.rp_lo);
-#pragma unroll
-            for (int i = 0; i < 4; i++) {      // R^T[j][p in sub-block i] = sum over q in sub-blocks <= i
-                const int rb = rev ? 3 - i : i;
-#pragma unroll
-                for (int s = 0; s <= i; s++) {
-                    const int kb = rev ? 3 - s : s;
-                    umma(tR + 16 * rb, desc_mn(a_kt + vbK[i] + kb * 2048), desc_k(a_qm + rb * 2048 + kb * 32), ID_MK16, s > 0);
-                    umma(tR + 16 * rb, desc_mn(a_ktl + vbK[i] + kb * 2048), desc_k(a_qm + rb * 2048 + kb * 32), ID_MK16, 1);
+            if (warp < 4) {
+                {   // R^T[j][p in sub-block i] = sum over q in sub-blocks <= i
+                    const int i = warp;
+                    const int rb = rev ? 3 - i : i;
+                    const int vbi = i == 0 ? vbK[0] : i == 1 ? vbK[1] : i == 2 ? vbK[2] : vbK[3];
+                    for (int s_ = 0; s_ <= i; s_++) {
+                        const int kb = rev ? 3 - s_ : s_;
+                        umma(tR + 16 * rb, dm_kt + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > 0);
+                        umma(tR + 16 * rb, dm_ktl + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
+                    }
                 }
-            }
-#pragma unroll
-            for (int j = 0; j < 4; j++) {      // K^T[j][q in sub-block j] = sum over p in sub-blocks >= j
-                const int rb = rev ? 3 - j : j;
-#pragma unroll
-                for (int s = j; s < 4; s++) {
-                    const int kb = rev ? 3 - s : s;
-                    umma(tK + 16 * rb, desc_mn(a_rp + vbR[j] + kb * 2048), desc_k(a_qmt + rb * 2048 + kb * 32), ID_MK16, s > j);
-                    umma(tK + 16 * rb, desc_mn(a_rpl + vbR[j] + kb * 2048), desc_k(a_qmt + rb * 2048 + kb * 32), ID_MK16, 1);
+                {   // K^T[j][q in sub-block j] = sum over p in sub-blocks >= j
+                    const int j = warp;
+                    const int rb = rev ? 3 - j : j;
+                    const int vbj = j == 0 ? vbR[0] : j == 1 ? vbR[1] : j == 2 ? vbR[2] : vbR[3];
+                    for (int s_ = j; s_ < 4; s_++) {
+                        const int kb = rev ? 3 - s_ : s_;
+                        umma(tK + 16 * rb, dm_rp + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > j);
+                        umma(tK + 16 * rb, dm_rpl + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
+                    }
                 }
+            } else if (warp == 4) {
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++) umma(tGV, dk_pt + DOFF(ks * 32), dm_g + DOFF(ks * 2048), ID_KM64, ks > 0);
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++) umma(tGV, dk_kend + DOFF(ks * 32), dm_cp + DOFF(ks * 2048), ID_KM64, 1);
+            } else {
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++) umma(tDC, dm_rst + DOFF(ks * 2048), dm_g + DOFF(ks * 2048), ID_MM64, ks > 0);
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++) umma(tDC, dm_rstl + DOFF(ks * 2048), dm_g + DOFF(ks * 2048), ID_MM64, 1);
             }
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tGV, desc_k(a_pt + ks * 32), desc_mn(a_g + ks * 2048), ID_KM64, ks > 0);
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tGV, desc_k(a_kend + ks * 32), desc_mn(a_cp + ks * 2048), ID_KM64, 1);
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tDC, desc_mn(a_rst + ks * 2048), desc_mn(a_g + ks * 2048), ID_MM64, ks > 0);
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tDC, desc_mn(a_rstl + ks * 2048), desc_mn(a_g + ks * 2048), ID_MM64, 1);
             umma_commit(&sm.bar_m2);
         }
+        __syncwarp();
 
         // ================= E2: drain the phase-2 accumulators
+        WKV6_TS(64, 10);
         mbar_wait(&sm.bar_m2, par);
+        WKV6_TS(64, 11);
         tc_fence_after();
         if (tid == 0 && cb + 1 < nchunks) issue_vg(cb + 1);   // V, G are dead once the phase-2 MMAs have completed
         {
@@ -582,7 +576,9 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
             store_cp();
         }
+        WKV6_TS(64, 12);
         __syncthreads();   // B4: xr / xk / hst / vg visible; all TMEM reads of this chunk done
+        WKV6_TS(64, 13);
         if (tid == 0 && cb + 1 < nchunks) issue_sp(cb + 1);   // S_0 tile is dead after the anchor sum
 
         // ================= final epilogue (row-major): gr, gk, gu, gw
@@ -637,6 +633,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 for (int r = 0; r < 4; r++) pre[r][e] += ex;
                 if (rg == 3) sm.dtot[I][c0 + e] = x;
             }
+            WKV6_TS(64, 14);
             __syncthreads();   // B5: dtot visible
             float base[4];
 #pragma unroll
@@ -666,6 +663,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         }
         fence_proxy_async();
         tc_fence_before();
+        WKV6_TS(64, 15);
         __syncthreads();   // B6: staging tiles complete; raw tiles and xr/xk no longer needed
         if (tid == 0) {
             tma_store_3d(&D.mgr, o_gr, h * N, t0, b);
@@ -710,7 +708,9 @@ int launch_bwd_chunk(const Params& p, cudaStream_t st) {
     const size_t smem = sizeof(BwdChunkSmem) + 1024;
     cudaError_t e = cudaFuncSetAttribute(wkv6_bwd_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    wkv6_bwd_chunk_kernel<<<dim3(p.ndir * p.B * p.H), dim3(256), smem, st>>>(p);
+    Params q = p;
+    q.dbg = debug_trace_buffer();
+    wkv6_bwd_chunk_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), smem, st>>>(q);
     count_launch(1);
     return (int)cudaGetLastError();
 }

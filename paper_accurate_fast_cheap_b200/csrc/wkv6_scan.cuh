@@ -34,6 +34,7 @@ struct Params {
     int B, T, C, H;
     int ndir;
     int skip_y;                           // chunk forward: compute states/checkpoints only (backward recompute)
+    unsigned long long* dbg;              // optional clock64() trace of one CTA (wkv6_b200_debug_trace), else null
 };
 
 // launchers (wkv6_scan.cu / wkv6_chunk.cu); return cudaError_t as int
@@ -44,5 +45,14 @@ int launch_bwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05;
 int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out, cudaStream_t st);
 
 void count_launch(int n);
+unsigned long long* debug_trace_buffer();
+
+// clock64() of CTA 0 at chunk `WKV6_TS_CHUNK`: slots 0..15 thread 0 (MMA issuer), 16..31 thread 32
+#define WKV6_TS_CHUNK 4
+#define WKV6_TS(base, i)                                                                          \
+    do {                                                                                          \
+        if (p.dbg && blockIdx.x == 0 && (tid == 0 || tid == 32) && c_ts == WKV6_TS_CHUNK)         \
+            p.dbg[(base) + (tid ? 16 : 0) + (i)] = clock64();                                     \
+    } while (0)
 
 }  // namespace wkv6

@@ -72,4 +72,38 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 
+__device__ __forceinline__ void tmem_ld_16x32(uint32_t taddr, float (&v)[16]) {   // 16 lanes x 32 columns
+    uint32_t u[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]), "=r"(u[8]), "=r"(u[9]),
+          "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; i++) v[i] = __uint_as_float(u[i]);
+}
+
+__device__ __forceinline__ void ld4bf(const uint8_t* p, float (&f)[4]) {   // 4 consecutive bf16 -> fp32
+    const uint2 q = *reinterpret_cast<const uint2*>(p);
+    f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
+    f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
+}
+__device__ __forceinline__ void up4bf(const uint2 q, float (&f)[4]) {
+    f[0] = __uint_as_float(q.x << 16); f[1] = __uint_as_float(q.x & 0xffff0000u);
+    f[2] = __uint_as_float(q.y << 16); f[3] = __uint_as_float(q.y & 0xffff0000u);
+}
+__device__ __forceinline__ void st4bf(uint8_t* p, const float (&f)[4]) {
+    *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]));
+}
+// x = hi + lo with hi = bf16(x), lo = bf16(x - hi): two bf16 tiles carry ~16 mantissa bits through the MMA.  Needed
+// where two differently factorised sums must cancel (the gw prefix sum), see DESIGN.md.
+__device__ __forceinline__ void st4bf_hilo(uint8_t* hi, uint8_t* lo, const float (&f)[4]) {
+    const uint32_t h0 = pack_bf16(f[0], f[1]), h1 = pack_bf16(f[2], f[3]);
+    *reinterpret_cast<uint2*>(hi) = make_uint2(h0, h1);
+    const float l0 = f[0] - __uint_as_float(h0 << 16), l1 = f[1] - __uint_as_float(h0 & 0xffff0000u);
+    const float l2 = f[2] - __uint_as_float(h1 << 16), l3 = f[3] - __uint_as_float(h1 & 0xffff0000u);
+    *reinterpret_cast<uint2*>(lo) = make_uint2(pack_bf16(l0, l1), pack_bf16(l2, l3));
+}
+
 }  // namespace wkv6
