@@ -67,6 +67,7 @@ const char* wkv6_b200_last_error(void);
 long long wkv6_b200_launch_count(void);
 /* Debug aid: clock64() trace of one CTA of the chunk kernels (see csrc/wkv6_capi.cu); not part of the data path. */
 int  wkv6_b200_debug_trace(int enable, unsigned long long* out);
+int  wkv6_b200_debug_trace_ctas(unsigned long long* out);   /* 4*1024 entries: per-CTA {t_start, smid, t_end, 0} */
 void wkv6_b200_set_algo(int algo);
 int  wkv6_b200_get_algo(void);
 

@@ -282,16 +282,22 @@ using namespace wkv6;
 extern "C" {
 
 int wkv6_b200_abi_version(void) { return 2; }
-/* Debug: enable != 0 allocates a 128-slot device buffer that CTA 0 of the chunk kernels fills with clock64() stamps
- * (forward: slots 0..31, backward: 64..95); `out` (host, 128 entries) receives the current contents. */
+/* Debug: enable != 0 allocates a device buffer that CTA 0 of the chunk kernels fills with clock64() stamps (forward:
+ * slots 0..31, backward: 64..95) and, from slot 128 on, every CTA < 1024 of the forward chunk kernel with
+ * {globaltimer at start, SM id, globaltimer at end, 0}; `out` (host, 128 entries) receives the first 128 slots;
+ * wkv6_b200_debug_trace_ctas copies the per-CTA part (4 * 1024 entries). */
 int wkv6_b200_debug_trace(int enable, unsigned long long* out) {
     if (enable && !g_dbg) {
-        if (cudaMalloc(&g_dbg, 128 * sizeof(unsigned long long)) != cudaSuccess) return -1;
-        cudaMemset(g_dbg, 0, 128 * sizeof(unsigned long long));
+        if (cudaMalloc(&g_dbg, (128 + 4096) * sizeof(unsigned long long)) != cudaSuccess) return -1;
+        cudaMemset(g_dbg, 0, (128 + 4096) * sizeof(unsigned long long));
     }
     if (out && g_dbg) cudaMemcpy(out, g_dbg, 128 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     if (!enable && g_dbg) { cudaFree(g_dbg); g_dbg = nullptr; }
     return 0;
+}
+int wkv6_b200_debug_trace_ctas(unsigned long long* out) {
+    if (!out || !g_dbg) return -1;
+    return (int)cudaMemcpy(out, g_dbg + 128, 4096 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
 }
 size_t wkv6_b200_checkpoint_bytes(int B, int T, int C, int H) {
     (void)C;

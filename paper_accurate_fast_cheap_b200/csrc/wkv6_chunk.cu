@@ -9,7 +9,9 @@
 // the START of the row's sub-block I:  Rtil_p = r_p 2^(A_p - A_BI) (<= |r|),  Ktil(I)_q = k_q 2^(A_BI - A+_q)
 // (<= |k| for earlier sub-blocks, <= 2^(16*7.2) inside the diagonal sub-block: finite in bf16/fp32).
 //
-// One CTA (128 threads) per (direction, batch, head); two CTAs per SM overlap each other's TMA / MMA latency.
+// One CTA (256 threads) per (direction, batch, head); two CTAs per SM overlap each other's TMA / MMA latency.
+// This file holds the first version of the kernel (kept behind WKV6_FWD_CHUNK_V1 for A/B runs); the default is the
+// software-pipelined, packed-bf16 version in wkv6_chunk_lean.cu.
 //   G1 (x4): P^T[:, block I] = Ktil(I) [64 q x 64 j, K-major A]  x  Rtil[block I] [16 p x 64 j, K-major B]   M64 N16 K64
 //   G3     : Y   = Rst [64 p x 64 j, K-major A] x S' [64 j x 64 i, MN-major B]                              M64 N64 K64
 //   G2     : Y  += P^T tile [64 q x 64 p, MN-major A] x V [64 q x 64 i, MN-major B, straight from TMA]
@@ -22,335 +24,6 @@
 #include <cstdlib>
 
 namespace wkv6 {
-
-struct ChunkSmem {
-    alignas(1024) uint8_t raw_r[CL * 128];   // TMA landing tiles (bf16, swizzled)
-    alignas(1024) uint8_t raw_k[CL * 128];
-    alignas(1024) uint8_t raw_w[CL * 128];
-    alignas(1024) uint8_t v[2][CL * 128];    // V: MMA operand straight from TMA
-    alignas(1024) uint8_t roff[CL * 128];    // r 2^(A_p - A_BI)
-    alignas(1024) uint8_t rst[CL * 128];     // r 2^(A_p)
-    alignas(1024) uint8_t kt[28 * 1024];     // Ktil(0..4), rows beyond a variant's own are never written (compact)
-    alignas(1024) uint8_t pt[CL * 128];      // masked P^T [q][p]; reused as the y staging tile [p][i]
-    alignas(1024) uint8_t sp[N * 128];       // bf16 state operand S^T [j][i]
-    float blocktot[4][N];                    // log2-domain decay sums of the four sub-blocks, per channel
-    float bonus[CL];
-    alignas(8) uint64_t bar_rkw, bar_v[2], bar_p, bar_y;
-    uint32_t tmem_base;
-};
-
-__global__ void __launch_bounds__(128, 2) wkv6_fwd_chunk128_kernel(const __grid_constant__ Params p) {
-    extern __shared__ __align__(1024) uint8_t smem_bytes[];
-    // offset arithmetic on the __shared__ array (not a uintptr_t round trip) keeps the address space visible to the
-    // compiler: LDS/STS instead of generic LD/ST
-    ChunkSmem& sm = *reinterpret_cast<ChunkSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int BH = p.B * p.H;
-    const int ds = blockIdx.x / BH;
-    const int bh = blockIdx.x - ds * BH;
-    const int b = bh / p.H, h = bh - b * p.H;
-    const DirArgs& D = p.d[ds];
-    const bool rev = D.reverse != 0;
-    const int T = p.T;
-    const int nchunks = (T + CL - 1) / CL;
-
-    // Ktil variant tiles, compact: virtual base (row 0) of variant I inside sm.kt, per direction
-    const int vb0 = rev ? 20 * 1024 : 0, vb1 = rev ? 18 * 1024 : 2 * 1024, vb2 = rev ? 14 * 1024 : 6 * 1024,
-              vb3 = rev ? 0 : 12 * 1024, vb4 = rev ? 8 * 1024 : 20 * 1024;
-    const int vb[5] = {vb0, vb1, vb2, vb3, vb4};
-
-    if (tid == 0) {
-        mbar_init(&sm.bar_rkw, 1);
-        mbar_init(&sm.bar_v[0], 1);
-        mbar_init(&sm.bar_v[1], 1);
-        mbar_init(&sm.bar_p, 1);
-        mbar_init(&sm.bar_y, 1);
-        fence_barrier_init();
-        tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
-        tma_prefetch_desc(&D.my);
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-    // zero the Ktil region once: rows that are never written must still hold finite bf16 values
-    for (int i = tid; i < 28 * 1024 / 16; i += 128) reinterpret_cast<uint4*>(sm.kt)[i] = make_uint4(0, 0, 0, 0);
-
-    // fragment coordinates of this thread in every 64x64 accumulator (16x256b TMEM load)
-    const int frow = 16 * warp + (lane >> 2);   // and frow + 8
-    const int fcol = 2 * (lane & 3);            // + 8*rep + {0,1}
-
-    // state S^T[j][i], j = frow + 8*hh, i = 8*rep + fcol + e  ->  st[4*rep + 2*hh + e]
-    float st[32];
-    {
-        const float* s0 = D.s0 ? D.s0 + (size_t)bh * N * N : nullptr;
-#pragma unroll
-        for (int rep = 0; rep < 8; rep++)
-#pragma unroll
-            for (int hh = 0; hh < 2; hh++)
-#pragma unroll
-                for (int e = 0; e < 2; e++) {
-                    const int j = frow + 8 * hh, i = 8 * rep + fcol + e;
-                    st[4 * rep + 2 * hh + e] = s0 ? s0[i * N + j] : 0.f;
-                }
-    }
-    auto store_sp = [&]() {   // bf16 copy of the state as the MN-major B operand of G3
-#pragma unroll
-        for (int rep = 0; rep < 8; rep++)
-#pragma unroll
-            for (int hh = 0; hh < 2; hh++) {
-                const int j = frow + 8 * hh;
-                *reinterpret_cast<uint32_t*>(sm.sp + sw_chunk(j, rep) + fcol * 2) = pack_bf16(st[4 * rep + 2 * hh], st[4 * rep + 2 * hh + 1]);
-            }
-    };
-    store_sp();
-
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tbase = sm.tmem_base;
-    const uint32_t tP = tbase, tY = tbase + 64, tD = tbase + 128;
-    const uint32_t lane_field = (uint32_t)(warp * 32) << 16;
-
-    auto issue_tma = [&](int c) {   // thread 0 only
-        const int q = rev ? nchunks - 1 - c : c;
-        mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
-        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q * CL, b);
-        tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q * CL, b);
-        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q * CL, b);
-        mbar_arrive_expect_tx(&sm.bar_v[c & 1], (uint32_t)CL * 128);
-        tma_load_3d(sm.v[c & 1], &D.mv, &sm.bar_v[c & 1], h * N, q * CL, b);
-    };
-    if (tid == 0 && nchunks > 0) issue_tma(0);
-
-    // preprocessing coordinates: warp = 16-step sub-block (processing order), 4 steps x 8 channels per thread
-    const int cg = lane & 7, rg = lane >> 3;
-    float u8[8];
-    io_traits<__nv_bfloat16>::load8(reinterpret_cast<const __nv_bfloat16*>(D.u) + h * N + cg * 8, u8);
-
-    constexpr uint32_t ID_G1 = umma_idesc(0, 0, 64, 16);
-    constexpr uint32_t ID_G2 = umma_idesc(1, 1, 64, 64);
-    constexpr uint32_t ID_G3 = umma_idesc(0, 1, 64, 64);
-
-    for (int c = 0; c < nchunks; c++) {
-        const int q = rev ? nchunks - 1 - c : c;
-        const int t0 = q * CL;
-        if (tid == 0) tma_store_wait_read<0>();   // the y staging tile (= pt) of the previous chunk has been read
-
-        // ---------------- phase 1: decays, in-block cumulative sums, Rtil, Ktil(own block), bonus
-        mbar_wait(&sm.bar_rkw, c & 1);
-        float roff[4][8], kb[4][8], l2[4][8], bsum[4];
-        int rows[4];
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-            const int pos = 16 * warp + 4 * rg + r;
-            const int row = rev ? 63 - pos : pos;
-            rows[r] = row;
-            const int off = sw_chunk(row, cg);
-            float w8[8];
-            io_traits<__nv_bfloat16>::load8(reinterpret_cast<const __nv_bfloat16*>(sm.raw_r + off), roff[r]);
-            io_traits<__nv_bfloat16>::load8(reinterpret_cast<const __nv_bfloat16*>(sm.raw_k + off), kb[r]);
-            io_traits<__nv_bfloat16>::load8(reinterpret_cast<const __nv_bfloat16*>(sm.raw_w + off), w8);
-            const bool valid = t0 + row < T;
-            float bs = 0.f;
-#pragma unroll
-            for (int e = 0; e < 8; e++) {
-                bs = fmaf(roff[r][e] * u8[e], kb[r][e], bs);
-                const float l = fmaxf(-ex2(w8[e] * kLog2e) * kLog2e, -kClampL2);
-                l2[r][e] = valid ? l : 0.f;
-            }
-            bsum[r] = bs;
-        }
-#pragma unroll
-        for (int e = 0; e < 8; e++) {   // inclusive sums over this thread's 4 steps
-            l2[1][e] += l2[0][e];
-            l2[2][e] += l2[1][e];
-            l2[3][e] += l2[2][e];
-        }
-        float excl[8];
-#pragma unroll
-        for (int e = 0; e < 8; e++) {   // scan over the 4 step-groups of the sub-block (lane bits 3,4)
-            float x = l2[3][e];
-            float y = __shfl_up_sync(0xffffffffu, x, 8);
-            if (rg >= 1) x += y;
-            y = __shfl_up_sync(0xffffffffu, x, 16);
-            if (rg >= 2) x += y;
-            excl[e] = x - l2[3][e];
-            if (rg == 3) sm.blocktot[warp][cg * 8 + e] = x;
-        }
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-#pragma unroll
-            for (int e = 0; e < 8; e++) {
-                const float aex = excl[e] + (r ? l2[r - 1][e] : 0.f);   // A_p - A_BI      (<= 0)
-                const float ain = excl[e] + l2[r][e];                   // A+_p - A_BI     (<= 0)
-                roff[r][e] *= ex2(aex);
-                kb[r][e] *= ex2(-ain);
-            }
-            io_traits<__nv_bfloat16>::store8(reinterpret_cast<__nv_bfloat16*>(sm.roff + sw_chunk(rows[r], cg)), roff[r]);
-            const float bs = sum_lanes8(bsum[r]);
-            if (cg == 0) sm.bonus[rows[r]] = bs;
-        }
-        __syncthreads();   // B1: blocktot/bonus visible, raw r/k/w consumed
-        if (tid == 0 && c + 1 < nchunks) issue_tma(c + 1);
-
-        // ---------------- phase 2: cross-block factors, Rst, Ktil variants
-        {
-            float s8[8];
-#pragma unroll
-            for (int e = 0; e < 8; e++) s8[e] = 0.f;
-            for (int m = 0; m < warp; m++) {
-                float t8[8];
-                ld8f(&sm.blocktot[m][cg * 8], t8);
-#pragma unroll
-                for (int e = 0; e < 8; e++) s8[e] += t8[e];
-            }
-#pragma unroll
-            for (int e = 0; e < 8; e++) s8[e] = ex2(s8[e]);   // 2^(A_BI)
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                float x8[8];
-#pragma unroll
-                for (int e = 0; e < 8; e++) x8[e] = roff[r][e] * s8[e];
-                io_traits<__nv_bfloat16>::store8(reinterpret_cast<__nv_bfloat16*>(sm.rst + sw_chunk(rows[r], cg)), x8);
-            }
-            float acc[8];
-#pragma unroll
-            for (int e = 0; e < 8; e++) acc[e] = 0.f;
-#pragma unroll
-            for (int I = 0; I <= 4; I++) {
-                if (I > warp) {
-                    float t8[8];
-                    ld8f(&sm.blocktot[I - 1][cg * 8], t8);
-#pragma unroll
-                    for (int e = 0; e < 8; e++) acc[e] += t8[e];
-                }
-                if (I >= warp) {
-                    float f8[8];
-#pragma unroll
-                    for (int e = 0; e < 8; e++) f8[e] = (I == warp) ? 1.f : ex2(acc[e]);   // 2^(A_B(I) - A_B(own))
-#pragma unroll
-                    for (int r = 0; r < 4; r++) {
-                        float x8[8];
-#pragma unroll
-                        for (int e = 0; e < 8; e++) x8[e] = kb[r][e] * f8[e];
-                        io_traits<__nv_bfloat16>::store8(reinterpret_cast<__nv_bfloat16*>(sm.kt + vb[I] + sw_chunk(rows[r], cg)), x8);
-                    }
-                }
-            }
-        }
-        fence_proxy_async();
-        tc_fence_before();
-        __syncthreads();   // B2: operand tiles complete
-        if (tid == 0) {
-            tc_fence_after();
-            if (D.ckpt) {   // S at the start of this chunk (bf16, [j][i]) -> checkpoint c of this sequence
-                tma_store_2d(&D.mc, sm.sp, 0, (bh * nchunks + c) * N);
-                tma_store_commit();
-            }
-            mbar_wait(&sm.bar_v[c & 1], (c >> 1) & 1);
-            const uint32_t a_rst = smem_u32(sm.rst), b_sp = smem_u32(sm.sp), a_kt = smem_u32(sm.kt), b_roff = smem_u32(sm.roff),
-                           b_v = smem_u32(sm.v[c & 1]);
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tY, desc_k(a_rst + ks * 32), desc_mn(b_sp + ks * 2048), ID_G3, ks > 0);
-#pragma unroll
-            for (int I = 0; I < 4; I++) {
-                const int rowlo = rev ? 48 - 16 * I : 16 * I;
-#pragma unroll
-                for (int ks = 0; ks < 4; ks++)
-                    umma(tP + rowlo, desc_k(a_kt + vb[I] + ks * 32), desc_k(b_roff + rowlo * 128 + ks * 32), ID_G1, ks > 0);
-            }
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tD, desc_mn(a_kt + vb[4] + ks * 2048), desc_mn(b_v + ks * 2048), ID_G2, ks > 0);
-            umma_commit(&sm.bar_p);
-        }
-
-        // ---------------- P^T readout: causal mask + bonus diagonal -> bf16 tile (MN-major A of G2)
-        mbar_wait(&sm.bar_p, c & 1);
-        tc_fence_after();
-        {
-            float pv[32];
-            tmem_ld_16x64(tP + lane_field, pv);
-#pragma unroll
-            for (int rep = 0; rep < 8; rep++)
-#pragma unroll
-                for (int hh = 0; hh < 2; hh++) {
-                    const int qq = frow + 8 * hh;
-                    float x[2];
-#pragma unroll
-                    for (int e = 0; e < 2; e++) {
-                        const int pp = 8 * rep + fcol + e;
-                        const bool before = rev ? (qq > pp) : (qq < pp);
-                        x[e] = before ? pv[4 * rep + 2 * hh + e] : (qq == pp ? sm.bonus[pp] : 0.f);
-                    }
-                    *reinterpret_cast<uint32_t*>(sm.pt + sw_chunk(qq, rep) + fcol * 2) = pack_bf16(x[0], x[1]);
-                }
-        }
-        fence_proxy_async();
-        tc_fence_before();
-        if (tid == 0 && D.ckpt) tma_store_wait_read<0>();   // sp is rewritten after B3
-        __syncthreads();   // B3: P^T tile complete
-        if (tid == 0) {
-            tc_fence_after();
-            const uint32_t a_pt = smem_u32(sm.pt), b_v = smem_u32(sm.v[c & 1]);
-#pragma unroll
-            for (int ks = 0; ks < 4; ks++) umma(tY, desc_mn(a_pt + ks * 2048), desc_mn(b_v + ks * 2048), ID_G2, 1);
-            umma_commit(&sm.bar_y);
-        }
-
-        // ---------------- state update (overlaps G2):  S^T[j][i] = S^T[j][i] 2^(A_L[j]) + dS^T[j][i]
-        {
-            float dv[32];
-            tmem_ld_16x64(tD + lane_field, dv);
-            const float f0 = ex2(sm.blocktot[0][frow] + sm.blocktot[1][frow] + sm.blocktot[2][frow] + sm.blocktot[3][frow]);
-            const float f1 = ex2(sm.blocktot[0][frow + 8] + sm.blocktot[1][frow + 8] + sm.blocktot[2][frow + 8] + sm.blocktot[3][frow + 8]);
-#pragma unroll
-            for (int rep = 0; rep < 8; rep++) {
-                st[4 * rep + 0] = fmaf(st[4 * rep + 0], f0, dv[4 * rep + 0]);
-                st[4 * rep + 1] = fmaf(st[4 * rep + 1], f0, dv[4 * rep + 1]);
-                st[4 * rep + 2] = fmaf(st[4 * rep + 2], f1, dv[4 * rep + 2]);
-                st[4 * rep + 3] = fmaf(st[4 * rep + 3], f1, dv[4 * rep + 3]);
-            }
-            store_sp();
-        }
-
-        // ---------------- Y readout -> bf16 staging tile -> TMA store
-        mbar_wait(&sm.bar_y, c & 1);
-        tc_fence_after();
-        {
-            float yv[32];
-            tmem_ld_16x64(tY + lane_field, yv);
-#pragma unroll
-            for (int rep = 0; rep < 8; rep++)
-#pragma unroll
-                for (int hh = 0; hh < 2; hh++)
-                    *reinterpret_cast<uint32_t*>(sm.pt + sw_chunk(frow + 8 * hh, rep) + fcol * 2) =
-                        pack_bf16(yv[4 * rep + 2 * hh], yv[4 * rep + 2 * hh + 1]);
-        }
-        fence_proxy_async();
-        tc_fence_before();
-        __syncthreads();   // B4: y tile complete; all TMEM reads of this chunk done
-        if (tid == 0 && !p.skip_y) {
-            tma_store_3d(&D.my, sm.pt, h * N, t0, b);
-            tma_store_commit();
-        }
-    }
-
-    if (tid == 0) tma_store_wait<0>();
-    if (D.sT) {
-        float* sT = D.sT + (size_t)bh * N * N;
-#pragma unroll
-        for (int rep = 0; rep < 8; rep++)
-#pragma unroll
-            for (int hh = 0; hh < 2; hh++)
-#pragma unroll
-                for (int e = 0; e < 2; e++) sT[(8 * rep + fcol + e) * N + frow + 8 * hh] = st[4 * rep + 2 * hh + e];
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tbase) : "memory");
-}
 
 // -------------------------------------------------------------------------------------------------------------------
 // 256-thread version: same algorithm and tiles, 8 warps per CTA and two CTAs per SM (<= 128 registers per thread), i.e.
@@ -722,21 +395,17 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_kernel(const __grid_con
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tbase) : "memory");
 }
 
+int launch_fwd_chunk_lean(const Params& p, cudaStream_t st);   // wkv6_chunk_lean.cu
+
 int launch_fwd_chunk(const Params& p, cudaStream_t st) {
-    static const bool use128 = getenv("WKV6_FWD_CHUNK128") != nullptr;   // A/B switch: the 128-thread kernel
-    if (use128) {
-        const size_t smem = sizeof(ChunkSmem) + 1024;
-        cudaError_t e = cudaFuncSetAttribute(wkv6_fwd_chunk128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        wkv6_fwd_chunk128_kernel<<<dim3(p.ndir * p.B * p.H), dim3(128), smem, st>>>(p);
-    } else {
-        const size_t smem = sizeof(Chunk256Smem) + 1024;
-        cudaError_t e = cudaFuncSetAttribute(wkv6_fwd_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        Params q = p;
-        q.dbg = debug_trace_buffer();
-        wkv6_fwd_chunk_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), smem, st>>>(q);
-    }
+    static const bool use_v1 = getenv("WKV6_FWD_CHUNK_V1") != nullptr;   // A/B switch: the first 256-thread kernel
+    if (!use_v1) return launch_fwd_chunk_lean(p, st);
+    const size_t smem = sizeof(Chunk256Smem) + 1024;
+    cudaError_t e = cudaFuncSetAttribute(wkv6_fwd_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    Params q = p;
+    q.dbg = debug_trace_buffer();
+    wkv6_fwd_chunk_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), smem, st>>>(q);
     count_launch(1);
     return (int)cudaGetLastError();
 }

@@ -1,0 +1,555 @@
+// wkv6_chunk_lean.cu -- chunked WKV6 forward (bf16 I/O) on tcgen05 / TMEM / TMA, second version (default).
+//
+// Same function, tiles and MMA groups as wkv6_chunk.cu (reference: wenet/rwkv_v6/cuda/wkv6_cuda.cu:9-63; chunked form
+// SURVEY.md App. A.5) -- read the header of that file for the algebra.  What changed, and why (the first version was
+// ISSUE-bound: ~1150 instructions per thread and chunk, 52 % issue utilisation, 4 CTA-wide barriers per chunk):
+//   * operand tiles are produced with packed bf16x2 arithmetic (HMUL2.BF16 on the raw TMA bits; the decay factors are
+//     computed in fp32, rounded once to bf16x2): no bf16->fp32 unpacking of r/k, half the multiplies, no F2FP per tile;
+//   * time direction is a template parameter: every row index, Ktil variant base and causal-mask predicate is a
+//     compile-time function of the thread coordinates;
+//   * the causal mask is resolved per 16x16 block (warp-uniform: keep / zero / diagonal), only diagonal blocks pay
+//     per-element selects;
+//   * TMEM fragments go to the swizzled operand tiles with stmatrix.x4 (2 per 16x32 fragment instead of 8 STS.32);
+//   * the chunk loop is software-pipelined: the tile building of chunk c+1 (which does not depend on the state) runs
+//     between the G2 issue and the Y readout of chunk c, so G2 / G3 / G4 latency is covered and only G1 -> P^T readout
+//     is exposed; 3 CTA-wide barriers per chunk.
+// Log-decays are kept with the opposite sign here (m = -l >= 0) so that the clamp is one FMNMX.
+#include "wkv6_umma.cuh"
+#include <cstdio>
+#include <cstdlib>
+
+namespace wkv6 {
+
+struct LeanSmem {
+    alignas(1024) uint8_t raw_r[CL * 128];   // TMA landing tiles (bf16, swizzled)
+    alignas(1024) uint8_t raw_k[CL * 128];
+    alignas(1024) uint8_t raw_w[CL * 128];
+    alignas(1024) uint8_t v[2][CL * 128];    // V: MMA operand straight from TMA
+    alignas(1024) uint8_t roff[CL * 128];    // r 2^(A_p - a_I)
+    alignas(1024) uint8_t rst[CL * 128];     // r 2^(A_p)
+    alignas(1024) uint8_t kt[28 * 1024];     // Ktil(0..4), compact (see wkv6_chunk.cu)
+    alignas(1024) uint8_t pt[CL * 128];      // masked P^T [q][p]
+    alignas(1024) uint8_t ys[CL * 128];      // y staging tile [p][i]
+    alignas(1024) uint8_t sp[N * 128];       // bf16 state operand S^T [j][i]; source of the checkpoint store
+    float blocktot[2][4][N];                 // -log2 decay sums of the four sub-blocks per channel, double-buffered
+    float bonus[2][CL];                      // sum_j r u k, one partial per channel half
+    alignas(8) uint64_t bar_rkw, bar_v[2], bar_p, bar_s, bar_y;
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint32_t bmul2(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t bfma2(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ void stsm_x4(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("stmatrix.sync.aligned.m8n8.x4.shared.b16 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d)
+                 : "memory");
+}
+__device__ __forceinline__ void sts64(uint32_t saddr, uint32_t a, uint32_t b) {
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(saddr), "r"(a), "r"(b) : "memory");
+}
+
+// one lane of a converged warp (the same one every time): MMA issue without a divergent-predicate waterfall loop
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}\n" : "=r"(pred));
+    return pred != 0;
+}
+
+constexpr float kLog2Log2e = 0.5287663729448977f;   // log2(log2(e)):  2^(w log2e + this) = e^w log2e
+
+// Ktil variant bases inside LeanSmem::kt (virtual row 0 of variant I), per direction
+template <bool REV>
+__device__ __forceinline__ constexpr int ktbase(int I) {
+    return REV ? (I == 0 ? 20 * 1024 : I == 1 ? 18 * 1024 : I == 2 ? 14 * 1024 : I == 3 ? 0 : 8 * 1024)
+               : (I == 0 ? 0 : I == 1 ? 2 * 1024 : I == 2 ? 6 * 1024 : I == 3 ? 12 * 1024 : 20 * 1024);
+}
+
+// phase 2 of one thread: cross-block factors -> Rst and the Ktil variants I+1..4 of this thread's 4 rows x 4 channels
+template <int I, bool REV>
+__device__ __forceinline__ void lean_phase2(uint32_t rst_u32, uint32_t kt_u32, const float* bt, int c0, const int (&offs)[4],
+                                            const uint32_t (&ro2)[4][2], const uint32_t (&ko2)[4][2]) {
+    float tot[4][4];
+#pragma unroll
+    for (int m = 0; m < 4; m++) {
+        const float4 t = *reinterpret_cast<const float4*>(bt + m * N + c0);
+        tot[m][0] = t.x; tot[m][1] = t.y; tot[m][2] = t.z; tot[m][3] = t.w;
+    }
+    if (I == 0) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) sts64(rst_u32 + offs[r], ro2[r][0], ro2[r][1]);
+    } else {
+        float f[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            float s = 0.f;
+#pragma unroll
+            for (int m = 0; m < I; m++) s += tot[m][e];
+            f[e] = ex2(-s);                     // 2^(a_I)
+        }
+        const uint32_t f0 = pack_bf16(f[0], f[1]), f1 = pack_bf16(f[2], f[3]);
+#pragma unroll
+        for (int r = 0; r < 4; r++) sts64(rst_u32 + offs[r], bmul2(ro2[r][0], f0), bmul2(ro2[r][1], f1));
+    }
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int m = I; m < 4; m++) {
+        float f[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            acc[e] += tot[m][e];
+            f[e] = ex2(-acc[e]);                // 2^(a_{m+1} - a_I)
+        }
+        const uint32_t f0 = pack_bf16(f[0], f[1]), f1 = pack_bf16(f[2], f[3]);
+        const uint32_t base = kt_u32 + ktbase<REV>(m + 1);
+#pragma unroll
+        for (int r = 0; r < 4; r++) sts64(base + offs[r], bmul2(ko2[r][0], f0), bmul2(ko2[r][1], f1));
+    }
+}
+
+template <bool REV>
+__device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const DirArgs& D, const int b, const int h, const int bh) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    // warp index through a lane-0 broadcast: the compiler then keeps it (and everything derived from it: MMA operands,
+    // descriptors, role branches) in uniform registers; a plain tid >> 5 makes every UTCHMMA a waterfall loop
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int T = p.T;
+    const int nchunks = (T + CL - 1) / CL;
+    // one elected lane of warp 5 issues every TMA load / store; one elected lane of warps 0..4 issues the MMAs
+#define TMA_THR (warp == 5 && elect_one())
+
+    if (tid == 0) {
+        mbar_init(&sm.bar_rkw, 1);
+        mbar_init(&sm.bar_v[0], 1);
+        mbar_init(&sm.bar_v[1], 1);
+        mbar_init(&sm.bar_p, 4);      // the four G1 groups are issued by four warps' lane 0 in parallel
+        mbar_init(&sm.bar_s, 1);
+        mbar_init(&sm.bar_y, 1);
+        fence_barrier_init();
+    }
+    if (TMA_THR) {
+        tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
+        if (!p.skip_y) tma_prefetch_desc(&D.my);
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // rows of a Ktil variant that are never written must still hold finite bf16 values
+    for (int i = tid; i < 28 * 1024 / 16; i += 256) reinterpret_cast<uint4*>(sm.kt)[i] = make_uint4(0, 0, 0, 0);
+
+    // TMEM fragment coordinates (16x256b.x4): rows frow, frow+8; columns fcol + 8*rep + {0,1}
+    const int qtr = warp & 3, half = warp >> 2;
+    const int frow = 16 * qtr + (lane >> 2);
+    const int fcol = 32 * half + 2 * (lane & 3);
+    const uint32_t lane_field = (uint32_t)(qtr * 32) << 16;
+    // stmatrix row addresses of this lane for the two x4 stores of a 16x32 fragment: matrix mi = lane>>3 of store s is
+    // (rep = 2s + (mi>>1), hh = mi&1), i.e. registers pk[4s .. 4s+3] in order
+    uint32_t stoff[2];
+    {
+        const int mi = lane >> 3, rr = lane & 7;
+        const int row = 16 * qtr + 8 * (mi & 1) + rr;
+        stoff[0] = (uint32_t)sw_chunk(row, 4 * half + (mi >> 1));
+        stoff[1] = (uint32_t)sw_chunk(row, 4 * half + 2 + (mi >> 1));
+    }
+    // row-major coordinates: sub-block I (in processing order), channels c0..c0+3, rows 4*rg..4*rg+3 of the sub-block
+    const int I = warp & 3, ch = warp >> 2;
+    const int cq = lane & 7, rg = lane >> 3;
+    const int c0 = 32 * ch + 4 * cq;
+    int offs[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        const int pos = 16 * I + 4 * rg + r;
+        const int row = REV ? 63 - pos : pos;
+        offs[r] = sw_chunk(row, c0 >> 3) + (c0 & 7) * 2;
+    }
+    const int vb_own = I == 0 ? ktbase<REV>(0) : I == 1 ? ktbase<REV>(1) : I == 2 ? ktbase<REV>(2) : ktbase<REV>(3);
+    const uint2 u2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(D.u) + (h * N + c0) * 2);
+
+    const uint32_t rawr_u32 = smem_u32(sm.raw_r), rawk_u32 = smem_u32(sm.raw_k), raww_u32 = smem_u32(sm.raw_w);
+    const uint32_t roff_u32 = smem_u32(sm.roff), rst_u32 = smem_u32(sm.rst), kt_u32 = smem_u32(sm.kt);
+    const uint32_t pt_u32 = smem_u32(sm.pt), ys_u32 = smem_u32(sm.ys), sp_u32 = smem_u32(sm.sp);
+
+    // state S^T[j][i]: j = frow + 8*hh, i = fcol + 8*rep + e  ->  st[4*rep + 2*hh + e]
+    float st[16];
+    {
+        const float* s0 = D.s0 ? D.s0 + (size_t)bh * N * N : nullptr;
+#pragma unroll
+        for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                for (int e = 0; e < 2; e++)
+                    st[4 * rep + 2 * hh + e] = s0 ? s0[(fcol + 8 * rep + e) * N + frow + 8 * hh] : 0.f;
+    }
+    auto store_frag = [&](uint32_t tile_u32, const float (&x)[16]) {   // fp32 fragment -> bf16 swizzled tile
+        uint32_t pk[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) pk[i] = pack_bf16(x[2 * i], x[2 * i + 1]);
+        stsm_x4(tile_u32 + stoff[0], pk[0], pk[1], pk[2], pk[3]);
+        stsm_x4(tile_u32 + stoff[1], pk[4], pk[5], pk[6], pk[7]);
+    };
+    store_frag(sp_u32, st);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
+    const uint32_t tP = tbase, tY = tbase + 64, tD = tbase + 128;
+
+    auto issue_rkw = [&](int c) {   // TMA_THR only
+        const int q = REV ? nchunks - 1 - c : c;
+        mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
+        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q * CL, b);
+        tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q * CL, b);
+        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q * CL, b);
+    };
+    auto issue_v = [&](int c) {
+        const int q = REV ? nchunks - 1 - c : c;
+        mbar_arrive_expect_tx(&sm.bar_v[c & 1], (uint32_t)CL * 128);
+        tma_load_3d(sm.v[c & 1], &D.mv, &sm.bar_v[c & 1], h * N, q * CL, b);
+    };
+
+    // UMMA smem descriptors built once; inside the loop: base + (byte offset >> 4)
+    const uint64_t dk_rst = desc_k(rst_u32), dk_kt = desc_k(kt_u32), dk_roff = desc_k(roff_u32);
+    const uint64_t dm_sp = desc_mn(sp_u32), dm_kt = desc_mn(kt_u32), dm_pt = desc_mn(pt_u32),
+                   dm_v0 = desc_mn(smem_u32(sm.v[0])), dm_v1 = desc_mn(smem_u32(sm.v[1]));
+#define DOFF(bytes) ((uint64_t)((bytes) >> 4))
+    constexpr uint32_t ID_G1 = umma_idesc(0, 0, 64, 16);
+    constexpr uint32_t ID_G2 = umma_idesc(1, 1, 64, 64);
+    constexpr uint32_t ID_G3 = umma_idesc(0, 1, 64, 64);
+
+    uint32_t ro2[4][2], ko2[4][2];   // Rtil / Ktil(own) of this thread's 4 rows x 4 channels, packed bf16x2
+
+    // ---- phase 1 of chunk c: decays, in-block cumulative sums, Rtil, Ktil(own block), bonus
+    auto phase1 = [&](const int c) {
+        const int q = REV ? nchunks - 1 - c : c;
+        const int t0 = q * CL;
+        mbar_wait(&sm.bar_rkw, c & 1);
+        float m[4][4];
+        uint32_t rr[4][2], kk[4][2];
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            uint2 ww;
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(rr[r][0]), "=r"(rr[r][1]) : "r"(rawr_u32 + offs[r]));
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(kk[r][0]), "=r"(kk[r][1]) : "r"(rawk_u32 + offs[r]));
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(ww.x), "=r"(ww.y) : "r"(raww_u32 + offs[r]));
+            float w4[4];
+            up4bf(ww, w4);
+#pragma unroll
+            for (int e = 0; e < 4; e++) m[r][e] = fminf(ex2(fmaf(w4[e], kLog2e, kLog2Log2e)), kClampL2);
+        }
+        if (t0 + CL > T) {   // ragged last chunk (CTA-uniform): steps at or beyond T neither decay nor contribute
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int pos = 16 * I + 4 * rg + r;
+                const int row = REV ? 63 - pos : pos;
+                if (t0 + row >= T) {
+#pragma unroll
+                    for (int e = 0; e < 4; e++) m[r][e] = 0.f;
+                }
+            }
+        }
+        // bonus sum_j r u k over this thread's 4 channels (packed bf16), then a transposing reduction over the 8 lanes
+        float bs[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            uint32_t a = bmul2(bmul2(rr[r][0], u2.x), kk[r][0]);
+            a = bfma2(bmul2(rr[r][1], u2.y), kk[r][1], a);
+            bs[r] = __uint_as_float(a << 16) + __uint_as_float(a & 0xffff0000u);
+        }
+        {
+            const bool b4 = (cq & 4) != 0, b2 = (cq & 2) != 0;
+            float k0 = b4 ? bs[2] : bs[0], k1 = b4 ? bs[3] : bs[1];
+            const float s0_ = b4 ? bs[0] : bs[2], s1_ = b4 ? bs[1] : bs[3];
+            k0 += __shfl_xor_sync(0xffffffffu, s0_, 4);
+            k1 += __shfl_xor_sync(0xffffffffu, s1_, 4);
+            float kk_ = b2 ? k1 : k0;
+            const float ss_ = b2 ? k0 : k1;
+            kk_ += __shfl_xor_sync(0xffffffffu, ss_, 2);
+            kk_ += __shfl_xor_sync(0xffffffffu, kk_, 1);
+            if ((cq & 1) == 0) {
+                const int pos = 16 * I + 4 * rg + (b4 ? 2 : 0) + (b2 ? 1 : 0);
+                sm.bonus[ch][REV ? 63 - pos : pos] = kk_;
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; e++) {   // inclusive sums over this thread's 4 steps
+            m[1][e] += m[0][e];
+            m[2][e] += m[1][e];
+            m[3][e] += m[2][e];
+        }
+        float excl[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {   // scan over the 4 step-groups of the sub-block (lane bits 3, 4)
+            float x = m[3][e];
+            float y = __shfl_up_sync(0xffffffffu, x, 8);
+            if (rg >= 1) x += y;
+            y = __shfl_up_sync(0xffffffffu, x, 16);
+            if (rg >= 2) x += y;
+            excl[e] = x - m[3][e];
+            m[3][e] = x;                // inclusive total up to and including this thread's last step
+        }
+        if (rg == 3) *reinterpret_cast<float4*>(&sm.blocktot[c & 1][I][c0]) = make_float4(m[3][0], m[3][1], m[3][2], m[3][3]);
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            float fr[4], fk[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float aex = r ? excl[e] + m[r - 1][e] : excl[e];          // -(A_p  - a_I) >= 0
+                const float ain = r == 3 ? m[3][e] : excl[e] + m[r][e];         // -(A+_p - a_I) >= 0
+                fr[e] = ex2(-aex);
+                fk[e] = ex2(ain);
+            }
+            ro2[r][0] = bmul2(rr[r][0], pack_bf16(fr[0], fr[1]));
+            ro2[r][1] = bmul2(rr[r][1], pack_bf16(fr[2], fr[3]));
+            ko2[r][0] = bmul2(kk[r][0], pack_bf16(fk[0], fk[1]));
+            ko2[r][1] = bmul2(kk[r][1], pack_bf16(fk[2], fk[3]));
+            sts64(roff_u32 + offs[r], ro2[r][0], ro2[r][1]);
+            sts64(kt_u32 + vb_own + offs[r], ko2[r][0], ko2[r][1]);
+        }
+    };
+    auto phase2 = [&](const int c) {
+        const float* bt = &sm.blocktot[c & 1][0][0];
+        switch (I) {   // warp-uniform
+            case 0: lean_phase2<0, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 1: lean_phase2<1, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 2: lean_phase2<2, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            default: lean_phase2<3, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+        }
+    };
+    // ---- MMAs that do not need P^T: G1 (four groups, four issuing lanes), G3 + G4 (one lane); checkpoint store
+    auto issue_front = [&](const int c) {
+        if (warp < 5 && elect_one()) {
+            tc_fence_after();
+            if (warp < 4) {
+                const int rowlo = REV ? 48 - 16 * warp : 16 * warp;
+                const int vbi = warp == 0 ? ktbase<REV>(0) : warp == 1 ? ktbase<REV>(1) : warp == 2 ? ktbase<REV>(2) : ktbase<REV>(3);
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++)
+                    umma(tP + rowlo, dk_kt + DOFF(vbi + ks * 32), dk_roff + DOFF(rowlo * 128 + ks * 32), ID_G1, ks > 0);
+                umma_commit(&sm.bar_p);
+            } else {
+                const uint64_t dm_v = (c & 1) ? dm_v1 : dm_v0;
+                mbar_wait(&sm.bar_v[c & 1], (c >> 1) & 1);
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++) umma(tY, dk_rst + DOFF(ks * 32), dm_sp + DOFF(ks * 2048), ID_G3, ks > 0);
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++)
+                    umma(tD, dm_kt + DOFF(ktbase<REV>(4) + ks * 2048), dm_v + DOFF(ks * 2048), ID_G2, ks > 0);
+                umma_commit(&sm.bar_s);
+            }
+        }
+        if (TMA_THR && D.ckpt) {   // S at the start of chunk c (bf16, [j][i]) -> checkpoint c of this sequence
+            tma_store_2d(&D.mc, sm.sp, 0, (bh * nchunks + c) * N);
+            tma_store_commit();
+        }
+        __syncwarp();
+    };
+
+    if (nchunks > 0) {
+        if (TMA_THR) { issue_rkw(0); issue_v(0); }
+        phase1(0);
+        __syncthreads();
+        if (TMA_THR && nchunks > 1) { issue_rkw(1); issue_v(1); }
+        phase2(0);
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        issue_front(0);
+    }
+
+    for (int c = 0; c < nchunks; c++) {
+        const int q = REV ? nchunks - 1 - c : c;
+        const int t0 = q * CL;
+        const uint32_t par = c & 1;
+        const bool more = c + 1 < nchunks;
+        const int c_ts = c;
+        WKV6_TS(0, 0);
+        if (p.dbg && blockIdx.x == 0 && tid == 0 && c < 32) p.dbg[32 + c] = clock64();   // loop-top stamp of every chunk
+
+        // ---------------- P^T readout: causal mask + bonus diagonal -> bf16 tile (MN-major A of G2)
+        mbar_wait(&sm.bar_p, par);
+        WKV6_TS(0, 1);
+        tc_fence_after();
+        {
+            float x[16];
+            tmem_ld_16x32(tP + lane_field + 32 * half, x);
+            uint32_t pk[8];
+#pragma unroll
+            for (int cb = 0; cb < 2; cb++) {   // the two 16-column blocks of this warp's 16x32 fragment
+                const int cls = REV ? qtr - (2 * half + cb) : (2 * half + cb) - qtr;   // warp-uniform
+                if (cls > 0) {          // every q before every p: keep
+#pragma unroll
+                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = pack_bf16(x[8 * cb + 2 * i], x[8 * cb + 2 * i + 1]);
+                } else if (cls < 0) {   // no q before any p
+#pragma unroll
+                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = 0u;
+                } else {                // diagonal block: strict triangle + bonus on the diagonal
+                    const int dbase = REV ? (lane >> 2) - 2 * (lane & 3) : 2 * (lane & 3) - (lane >> 2);
+                    float bon[2];
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) bon[hh] = sm.bonus[0][frow + 8 * hh] + sm.bonus[1][frow + 8 * hh];
+#pragma unroll
+                    for (int rl = 0; rl < 2; rl++)
+#pragma unroll
+                        for (int hh = 0; hh < 2; hh++) {
+                            float y[2];
+#pragma unroll
+                            for (int e = 0; e < 2; e++) {
+                                const int d = dbase + (REV ? 8 * hh - 8 * rl - e : 8 * rl + e - 8 * hh);   // > 0: q before p
+                                const float xv = x[4 * (2 * cb + rl) + 2 * hh + e];
+                                y[e] = d > 0 ? xv : (d == 0 ? bon[hh] : 0.f);
+                            }
+                            pk[2 * (2 * cb + rl) + hh] = pack_bf16(y[0], y[1]);
+                        }
+                }
+            }
+            stsm_x4(pt_u32 + stoff[0], pk[0], pk[1], pk[2], pk[3]);
+            stsm_x4(pt_u32 + stoff[1], pk[4], pk[5], pk[6], pk[7]);
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        if (TMA_THR) tma_store_wait_read<0>();   // checkpoint c has left sp, y of chunk c-1 has left ys
+        WKV6_TS(0, 2);
+        __syncthreads();   // B3: P^T tile complete
+        WKV6_TS(0, 3);
+        if (warp == 4 && elect_one()) {
+            tc_fence_after();
+            const uint64_t dm_v = (c & 1) ? dm_v1 : dm_v0;
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tY, dm_pt + DOFF(ks * 2048), dm_v + DOFF(ks * 2048), ID_G2, 1);
+            umma_commit(&sm.bar_y);
+        }
+        __syncwarp();
+
+        // ---------------- state update (under G2):  S^T[j][i] = S^T[j][i] 2^(A_L[j]) + dS^T[j][i]
+        mbar_wait(&sm.bar_s, par);
+        WKV6_TS(0, 4);
+        tc_fence_after();
+        {
+            float dv[16];
+            tmem_ld_16x32(tD + lane_field + 32 * half, dv);
+            const float* bt = &sm.blocktot[par][0][0];
+            const float f0 = ex2(-((bt[frow] + bt[N + frow]) + (bt[2 * N + frow] + bt[3 * N + frow])));
+            const float f1 = ex2(-((bt[frow + 8] + bt[N + frow + 8]) + (bt[2 * N + frow + 8] + bt[3 * N + frow + 8])));
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++) {
+                st[4 * rep + 0] = fmaf(st[4 * rep + 0], f0, dv[4 * rep + 0]);
+                st[4 * rep + 1] = fmaf(st[4 * rep + 1], f0, dv[4 * rep + 1]);
+                st[4 * rep + 2] = fmaf(st[4 * rep + 2], f1, dv[4 * rep + 2]);
+                st[4 * rep + 3] = fmaf(st[4 * rep + 3], f1, dv[4 * rep + 3]);
+            }
+            store_frag(sp_u32, st);
+        }
+        WKV6_TS(0, 5);
+
+        // ---------------- tile building of the NEXT chunk (independent of the state; covers G2)
+        if (more) {
+            phase1(c + 1);
+            WKV6_TS(0, 6);
+            __syncthreads();   // B1: blocktot / bonus visible, raw r/k/w consumed
+            WKV6_TS(0, 7);
+            if (TMA_THR && c + 2 < nchunks) issue_rkw(c + 2);
+            phase2(c + 1);
+            WKV6_TS(0, 8);
+        }
+
+        // ---------------- Y readout -> bf16 staging tile -> TMA store
+        mbar_wait(&sm.bar_y, par);
+        WKV6_TS(0, 9);
+        tc_fence_after();
+        if (!p.skip_y) {
+            float yv[16];
+            tmem_ld_16x32(tY + lane_field + 32 * half, yv);
+            store_frag(ys_u32, yv);
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        WKV6_TS(0, 10);
+        __syncthreads();   // B2: y tile, sp and the operand tiles of chunk c+1 complete; TMEM reads of chunk c done
+        WKV6_TS(0, 11);
+        if (TMA_THR) {
+            if (!p.skip_y) {
+                tma_store_3d(&D.my, sm.ys, h * N, t0, b);
+                tma_store_commit();
+            }
+            if (c + 2 < nchunks) issue_v(c + 2);   // v[c&1] is free: G2 and G4 of chunk c have completed
+        }
+        if (more) issue_front(c + 1);
+        WKV6_TS(0, 12);
+    }
+
+    __syncwarp();
+    if (TMA_THR) tma_store_wait<0>();
+    if (D.sT) {
+        float* sT = D.sT + (size_t)bh * N * N;
+#pragma unroll
+        for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) sT[(fcol + 8 * rep + e) * N + frow + 8 * hh] = st[4 * rep + 2 * hh + e];
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tbase) : "memory");
+#undef DOFF
+#undef TMA_THR
+}
+
+__global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __grid_constant__ Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_bytes[];
+    // offset arithmetic on the __shared__ array (not a uintptr_t round trip) keeps the address space visible to the
+    // compiler: LDS/STS instead of generic LD/ST
+    LeanSmem& sm = *reinterpret_cast<LeanSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
+    const int BH = p.B * p.H;
+    const int ds = blockIdx.x / BH;
+    const int bh = blockIdx.x - ds * BH;
+    const int b = bh / p.H, h = bh - b * p.H;
+    const DirArgs& D = p.d[ds];
+    if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
+        unsigned long long t;
+        uint32_t smid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        p.dbg[128 + 4 * blockIdx.x] = t;
+        p.dbg[129 + 4 * blockIdx.x] = smid;
+    }
+    if (D.reverse) lean_body<true>(p, sm, D, b, h, bh);
+    else lean_body<false>(p, sm, D, b, h, bh);
+    if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.dbg[130 + 4 * blockIdx.x] = t;
+    }
+}
+
+int launch_fwd_chunk_lean(const Params& p, cudaStream_t st) {
+    const size_t smem = sizeof(LeanSmem) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(wkv6_fwd_chunk_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        cudaFuncSetAttribute(wkv6_fwd_chunk_lean_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        if (getenv("WKV6_DEBUG_OCC")) {
+            int nb = -1;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wkv6_fwd_chunk_lean_kernel, 256, smem);
+            fprintf(stderr, "[wkv6] fwd_chunk_lean: smem %zu B, resident CTAs/SM %d\n", smem, nb);
+        }
+        attr_set = true;
+    }
+    Params q = p;
+    q.dbg = debug_trace_buffer();
+    wkv6_fwd_chunk_lean_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), smem, st>>>(q);
+    count_launch(1);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace wkv6

@@ -27,3 +27,30 @@ for name, base, n in (("fwd", 0, 15), ("bwd", 64, 16)):
         t0 = ts[0]
         print(name, who, " ".join(f"{i}:{(x - t0) if x else -1}" for i, x in enumerate(ts)))
 L.wkv6_b200_debug_trace(0, None)
+
+# ---- per-CTA timeline of the forward chunk kernel (globaltimer ns): residency per SM, wave structure
+L.wkv6_b200_debug_trace(1, None)
+pk.bi_forward_raw(f, r_)
+torch.cuda.synchronize()
+cb = (ctypes.c_ulonglong * 4096)()
+L.wkv6_b200_debug_trace_ctas(cb)
+L.wkv6_b200_debug_trace(1, buf)
+v = list(buf)
+print("fwd loop tops (cycles since chunk 0):", " ".join(str(x - v[32]) for x in v[32:32 + 12]))
+L.wkv6_b200_debug_trace(0, None)
+rows = [(cb[4 * i], cb[4 * i + 1], cb[4 * i + 2]) for i in range(2 * B * H) if cb[4 * i]]
+if rows:
+    t_min = min(r[0] for r in rows); t_max = max(r[2] for r in rows)
+    durs = sorted(r[2] - r[0] for r in rows)
+    starts = sorted(r[0] - t_min for r in rows)
+    per_sm = {}
+    for s, sm, e in rows:
+        per_sm.setdefault(sm, []).append((s - t_min, e - t_min))
+    overlap2 = sum(1 for v in per_sm.values() if len(v) >= 2 and sorted(v)[1][0] < sorted(v)[0][1])
+    solo = sorted(v[0][1] - v[0][0] for v in per_sm.values() if len(v) == 1)
+    pair = sorted(e - s for v in per_sm.values() if len(v) == 2 for s, e in v)
+    if solo and pair:
+        print(f"solo CTA ns min/med/max {solo[0]}/{solo[len(solo)//2]}/{solo[-1]}; paired CTA ns {pair[0]}/{pair[len(pair)//2]}/{pair[-1]}; cta0 {rows[0][2]-rows[0][0]}")
+    print(f"ctas {len(rows)} span {t_max - t_min} ns; cta duration min/med/max {durs[0]}/{durs[len(durs)//2]}/{durs[-1]} ns; "
+          f"SMs used {len(per_sm)}, SMs with 2 CTAs {sum(1 for v in per_sm.values() if len(v) >= 2)}, overlapping in time {overlap2}; "
+          f"last start {starts[-1]} ns")
