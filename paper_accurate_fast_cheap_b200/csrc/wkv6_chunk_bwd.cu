@@ -68,7 +68,10 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     // compiler: LDS/STS instead of generic LD/ST
     BwdChunkSmem& sm = *reinterpret_cast<BwdChunkSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // warp index through a lane-0 broadcast: keeps MMA operands / role branches in uniform registers (a plain tid >> 5
+    // turns every UTCHMMA into a waterfall loop of R2UR broadcasts)
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int BH = p.B * p.H;
     const int ds = blockIdx.x / BH;
     const int bh = blockIdx.x - ds * BH;
@@ -152,7 +155,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tbase = sm.tmem_base;
+    const uint32_t tbase = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
     const uint32_t tQ = tbase, tP = tbase + 64, tRS = tbase + 128, tKC = tbase + 192, tR = tbase + 256, tK = tbase + 320,
                    tGV = tbase + 384, tDC = tbase + 448;
 
@@ -203,7 +206,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         const int c_ts = cb;
         WKV6_TS(64, 0);
         if (tid == 0) tma_store_wait_read<0>();          // staging tiles of the previous chunk have been read
-        if (lane == 0 && warp < 3) {
+        if (warp < 3 && elect_one()) {
             // ---- MMA phase 1a: everything that needs no preprocessing (V, G, S_0, C are raw / carried tiles)
             mbar_wait(&sm.bar_vg, par);
             mbar_wait(&sm.bar_sp, par);
@@ -357,7 +360,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             WKV6_TS(64, 4);
 
             // ================= MMA phase 1b: P^T (runs under the R-side preprocessing below)
-            if (lane == 0 && warp < 4) {
+            if (warp < 4 && elect_one()) {
                 tc_fence_after();
                 const int i = warp;
                 const int rowlo = rev ? 48 - 16 * i : 16 * i;
@@ -366,9 +369,9 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 for (int ks = 0; ks < 4; ks++)
                     umma(tP + rowlo, dk_kt + DOFF(vbi + ks * 32), dk_roff + DOFF(rowlo * 128 + ks * 32), ID_KK16, ks > 0);
                 umma_commit(&sm.bar_mp);
-                if (tid == 0 && cb + 1 < nchunks) issue_rkw(cb + 1);
             }
             __syncwarp();
+            if (tid == 0 && cb + 1 < nchunks) issue_rkw(cb + 1);
 #pragma unroll
             for (int r = 0; r < 4; r++) {       // R side: needed by the phase-2 MMAs only
                 const int off = sw_chunk(rows[r], cchunk) + coff;
@@ -444,7 +447,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         WKV6_TS(64, 9);
 
         // ================= MMA phase 2: six issuing lanes (warps 0-3: R^T and K^T group w; warp 4: GV; warp 5: dC)
-        if (lane == 0 && warp < 6) {
+        if (warp < 6 && elect_one()) {
             tc_fence_after();
             if (warp < 4) {
                 {   // R^T[j][p in sub-block i] = sum over q in sub-blocks <= i

@@ -55,13 +55,6 @@ __device__ __forceinline__ void sts64(uint32_t saddr, uint32_t a, uint32_t b) {
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(saddr), "r"(a), "r"(b) : "memory");
 }
 
-// one lane of a converged warp (the same one every time): MMA issue without a divergent-predicate waterfall loop
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}\n" : "=r"(pred));
-    return pred != 0;
-}
-
 constexpr float kLog2Log2e = 0.5287663729448977f;   // log2(log2(e)):  2^(w log2e + this) = e^w log2e
 
 // Ktil variant bases inside LeanSmem::kt (virtual row 0 of variant I), per direction
