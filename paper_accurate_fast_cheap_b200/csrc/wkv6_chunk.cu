@@ -396,9 +396,14 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_kernel(const __grid_con
 }
 
 int launch_fwd_chunk_lean(const Params& p, cudaStream_t st);   // wkv6_chunk_lean.cu
+int launch_fwd_chunk_ws(const Params& p, cudaStream_t st);     // wkv6_chunk_ws.cu
 
 int launch_fwd_chunk(const Params& p, cudaStream_t st) {
     static const bool use_v1 = getenv("WKV6_FWD_CHUNK_V1") != nullptr;   // A/B switch: the first 256-thread kernel
+    // warp-specialised variant (dedicated issuer warp): faster for a CTA that has its SM to itself (31 vs 36 us on the
+    // bench workload), slower when two CTAs share an SM (long tail, 55 us) -- opt-in until that is understood
+    static const bool use_ws = getenv("WKV6_FWD_CHUNK_WS") != nullptr;
+    if (use_ws) return launch_fwd_chunk_ws(p, st);
     if (!use_v1) return launch_fwd_chunk_lean(p, st);
     const size_t smem = sizeof(Chunk256Smem) + 1024;
     cudaError_t e = cudaFuncSetAttribute(wkv6_fwd_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

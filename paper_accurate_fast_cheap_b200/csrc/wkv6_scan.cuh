@@ -34,6 +34,7 @@ struct Params {
     int B, T, C, H;
     int ndir;
     int skip_y;                           // chunk forward: compute states/checkpoints only (backward recompute)
+    int dir_interleave;                   // forward ws kernel: direction = blockIdx parity instead of blockIdx / (B*H)
     unsigned long long* dbg;              // optional clock64() trace of one CTA (wkv6_b200_debug_trace), else null
 };
 
