@@ -35,8 +35,8 @@ struct BwdChunkSmem {
     alignas(1024) uint8_t raw_r[CL * 128];   // TMA landing tiles (bf16, 128B swizzle), rows = time, cols = channel
     alignas(1024) uint8_t raw_k[CL * 128];
     alignas(1024) uint8_t raw_w[CL * 128];
-    alignas(1024) uint8_t v[CL * 128];       // V and G: MMA operands straight from TMA
-    alignas(1024) uint8_t g[CL * 128];
+    alignas(1024) uint8_t v[2][CL * 128];    // V and G: MMA operands straight from TMA, double-buffered (loaded a
+    alignas(1024) uint8_t g[2][CL * 128];    // whole chunk ahead)
     alignas(1024) uint8_t sp[N * 128];       // S_0^T [j][i] bf16 (checkpoint, TMA)
     alignas(1024) uint8_t cp[N * 128];       // C^T   [j][i] bf16 copy of the reverse state
     alignas(1024) uint8_t roff[CL * 128];    // r 2^(A_p - a_I)
@@ -56,7 +56,7 @@ struct BwdChunkSmem {
     float bonus[2][CL];                      // sum_j r u k per row (two channel halves)
     float vg[CL];                            // v_p . gy_p per row
     float gured[8][N / 2];
-    alignas(8) uint64_t bar_rkw, bar_vg, bar_sp, bar_m1, bar_mp, bar_m2;
+    alignas(8) uint64_t bar_rkw, bar_vg[2], bar_sp, bar_m1, bar_mp, bar_m2;
     uint32_t tmem_base;
 };
 static_assert(sizeof(BwdChunkSmem) <= 226 * 1024, "shared memory budget");
@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 
     if (tid == 0) {
         mbar_init(&sm.bar_rkw, 1);
-        mbar_init(&sm.bar_vg, 1);
+        mbar_init(&sm.bar_vg[0], 1);
+        mbar_init(&sm.bar_vg[1], 1);
         mbar_init(&sm.bar_sp, 1);
         mbar_init(&sm.bar_mp, 4);     // MMA groups are issued by several warps' lane 0 in parallel (an issue costs
         mbar_init(&sm.bar_m1, 3);     // ~50 cycles of dependent uniform-datapath work); every issuer commits
@@ -161,12 +162,12 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 
     // UMMA smem descriptors of every operand tile, built once: inside the chunk loop a descriptor is base + (byte
     // offset >> 4), one 64-bit add on the uniform datapath instead of a dozen dependent uniform ops per MMA.
-    const uint64_t dk_g = desc_k(smem_u32(sm.g)), dk_v = desc_k(smem_u32(sm.v)), dk_sp = desc_k(smem_u32(sm.sp)),
+    const uint64_t dk_g0 = desc_k(smem_u32(sm.g[0])), dk_v0 = desc_k(smem_u32(sm.v[0])), dk_sp = desc_k(smem_u32(sm.sp)),
                    dk_cp = desc_k(smem_u32(sm.cp)), dk_kt = desc_k(smem_u32(sm.kt)), dk_roff = desc_k(smem_u32(sm.roff)),
                    dk_qm = desc_k(smem_u32(sm.qm)), dk_qmt = desc_k(smem_u32(sm.qmt)), dk_pt = desc_k(smem_u32(sm.pt)),
                    dk_kend = desc_k(smem_u32(kend));
     const uint64_t dm_kt = desc_mn(smem_u32(sm.kt)), dm_ktl = desc_mn(smem_u32(sm.kt_lo)), dm_rp = desc_mn(smem_u32(sm.rp)),
-                   dm_rpl = desc_mn(smem_u32(sm.rp_lo)), dm_g = desc_mn(smem_u32(sm.g)), dm_cp = desc_mn(smem_u32(sm.cp)),
+                   dm_rpl = desc_mn(smem_u32(sm.rp_lo)), dm_g0 = desc_mn(smem_u32(sm.g[0])), dm_cp = desc_mn(smem_u32(sm.cp)),
                    dm_rst = desc_mn(smem_u32(sm.rst)), dm_rstl = desc_mn(smem_u32(sm.rst_lo));
 #define DOFF(bytes) ((uint64_t)((bytes) >> 4))
 
@@ -182,9 +183,9 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     };
     auto issue_vg = [&](int cb) {
         const int q = tile_q(cb);
-        mbar_arrive_expect_tx(&sm.bar_vg, 2u * CL * 128);
-        tma_load_3d(sm.v, &D.mv, &sm.bar_vg, h * N, q * CL, b);
-        tma_load_3d(sm.g, &D.mg, &sm.bar_vg, h * N, q * CL, b);
+        mbar_arrive_expect_tx(&sm.bar_vg[cb & 1], 2u * CL * 128);
+        tma_load_3d(sm.v[cb & 1], &D.mv, &sm.bar_vg[cb & 1], h * N, q * CL, b);
+        tma_load_3d(sm.g[cb & 1], &D.mg, &sm.bar_vg[cb & 1], h * N, q * CL, b);
     };
     auto issue_sp = [&](int cb) {
         mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
@@ -203,12 +204,17 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         const int q = rev ? nchunks - 1 - c : c;         // tile index in memory
         const int t0 = q * CL;
         const uint32_t par = cb & 1;
+        const uint64_t vgoff = (cb & 1) ? DOFF(CL * 128) : 0;   // V / G buffer of this chunk (v[1] - v[0] = g[1] - g[0] = 8 KB)
+        const uint64_t dk_g = dk_g0 + vgoff, dk_v = dk_v0 + vgoff, dm_g = dm_g0 + vgoff;
         const int c_ts = cb;
         WKV6_TS(64, 0);
-        if (tid == 0) tma_store_wait_read<0>();          // staging tiles of the previous chunk have been read
+        // staging tiles of the previous chunk have been read (they alias operand tiles that are rewritten after the next
+        // CTA-wide barrier).  The store thread is warp 7 lane 0: it issues no MMAs, so this wait delays nobody.
+        if (tid == 224) tma_store_wait_read<0>();
+        if (tid == 0 && cb + 1 < nchunks) issue_vg(cb + 1);   // other V / G buffer: its readers finished last iteration
         if (warp < 3 && elect_one()) {
             // ---- MMA phase 1a: everything that needs no preprocessing (V, G, S_0, C are raw / carried tiles)
-            mbar_wait(&sm.bar_vg, par);
+            mbar_wait(&sm.bar_vg[cb & 1], (cb >> 1) & 1);
             mbar_wait(&sm.bar_sp, par);
             tc_fence_after();
             if (warp == 0) {
@@ -490,7 +496,6 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         mbar_wait(&sm.bar_m2, par);
         WKV6_TS(64, 11);
         tc_fence_after();
-        if (tid == 0 && cb + 1 < nchunks) issue_vg(cb + 1);   // V, G are dead once the phase-2 MMAs have completed
         {
             // per-thread decay factors of its two rows j (log2 sums of the sub-block totals)
             float t0j[4], t1j[4];
@@ -668,7 +673,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         tc_fence_before();
         WKV6_TS(64, 15);
         __syncthreads();   // B6: staging tiles complete; raw tiles and xr/xk no longer needed
-        if (tid == 0) {
+        if (tid == 224) {
             tma_store_3d(&D.mgr, o_gr, h * N, t0, b);
             tma_store_3d(&D.mgk, o_gk, h * N, t0, b);
             tma_store_3d(&D.mgv, o_gv, h * N, t0, b);
@@ -677,7 +682,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         }
     }
 
-    if (tid == 0) tma_store_wait<0>();
+    if (tid == 224) tma_store_wait<0>();
     // gu[b][h*64 + c] = sum over rows of r k (v.gy): row groups by shuffle, sub-blocks through smem
 #pragma unroll
     for (int e = 0; e < 4; e++) {
