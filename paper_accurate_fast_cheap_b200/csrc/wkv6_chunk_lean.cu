@@ -37,8 +37,10 @@ struct LeanSmem {
     uint32_t tmem_base;
 };
 
-template <bool REV>
-__device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const DirArgs& D, const int b, const int h, const int bh) {
+// REV is a RUNTIME flag on purpose: with the direction as a template parameter the two instantiations of co-resident CTAs
+// thrashed the instruction cache (ncu: "no instruction" top stall; 50.8 us mixed vs 45.6 us single-direction launches)
+__device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
+                                          const bool REV) {
     const int tid = threadIdx.x, lane = tid & 31;
     // warp index through a lane-0 broadcast: the compiler then keeps it (and everything derived from it: MMA operands,
     // descriptors, role branches) in uniform registers; a plain tid >> 5 makes every UTCHMMA a waterfall loop
@@ -93,7 +95,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         const int row = REV ? 63 - pos : pos;
         offs[r] = sw_chunk(row, c0 >> 3) + (c0 & 7) * 2;
     }
-    const int vb_own = I == 0 ? ktbase<REV>(0) : I == 1 ? ktbase<REV>(1) : I == 2 ? ktbase<REV>(2) : ktbase<REV>(3);
+    const int vb_own = I == 0 ? ktbase(REV, 0) : I == 1 ? ktbase(REV, 1) : I == 2 ? ktbase(REV, 2) : ktbase(REV, 3);
     const uint2 u2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(D.u) + (h * N + c0) * 2);
 
     const uint32_t rawr_u32 = smem_u32(sm.raw_r), rawk_u32 = smem_u32(sm.raw_k), raww_u32 = smem_u32(sm.raw_w);
@@ -242,10 +244,10 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
     auto phase2 = [&](const int c) {
         const float* bt = &sm.blocktot[c & 1][0][0];
         switch (I) {   // warp-uniform
-            case 0: lean_phase2<0, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 1: lean_phase2<1, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 2: lean_phase2<2, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            default: lean_phase2<3, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 0: lean_phase2<0>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 1: lean_phase2<1>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 2: lean_phase2<2>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            default: lean_phase2<3>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
         }
     };
     // ---- MMAs that do not need P^T: G1 (four groups, four issuing lanes), G3 + G4 (one lane); checkpoint store
@@ -254,7 +256,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             tc_fence_after();
             if (warp < 4) {
                 const int rowlo = REV ? 48 - 16 * warp : 16 * warp;
-                const int vbi = warp == 0 ? ktbase<REV>(0) : warp == 1 ? ktbase<REV>(1) : warp == 2 ? ktbase<REV>(2) : ktbase<REV>(3);
+                const int vbi = warp == 0 ? ktbase(REV, 0) : warp == 1 ? ktbase(REV, 1) : warp == 2 ? ktbase(REV, 2) : ktbase(REV, 3);
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++)
                     umma(tP + rowlo, dk_kt + DOFF(vbi + ks * 32), dk_roff + DOFF(rowlo * 128 + ks * 32), ID_G1, ks > 0);
@@ -266,7 +268,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
                 for (int ks = 0; ks < 4; ks++) umma(tY, dk_rst + DOFF(ks * 32), dm_sp + DOFF(ks * 2048), ID_G3, ks > 0);
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++)
-                    umma(tD, dm_kt + DOFF(ktbase<REV>(4) + ks * 2048), dm_v + DOFF(ks * 2048), ID_G2, ks > 0);
+                    umma(tD, dm_kt + DOFF(ktbase(REV, 4) + ks * 2048), dm_v + DOFF(ks * 2048), ID_G2, ks > 0);
                 umma_commit(&sm.bar_s);
             }
         }
@@ -446,8 +448,7 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
         p.dbg[128 + 4 * blockIdx.x] = t;
         p.dbg[129 + 4 * blockIdx.x] = smid;
     }
-    if (D.reverse) lean_body<true>(p, sm, D, b, h, bh);
-    else lean_body<false>(p, sm, D, b, h, bh);
+    lean_body(p, sm, D, b, h, bh, D.reverse != 0);
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

@@ -89,7 +89,7 @@ __device__ __forceinline__ void ws_issuer(const Params& p, WsSmem& sm, const Dir
             const int rowlo = REV ? 48 - 16 * i : 16 * i;
 #pragma unroll
             for (int ks = 0; ks < 4; ks++)
-                umma(tP + rowlo, dk_kt + DOFF(ktbase<REV>(i) + ks * 32), dk_roff + DOFF(rowlo * 128 + ks * 32), ID_G1, ks > 0);
+                umma(tP + rowlo, dk_kt + DOFF(ktbase(REV, i) + ks * 32), dk_roff + DOFF(rowlo * 128 + ks * 32), ID_G1, ks > 0);
         }
         umma_commit(&sm.bar_p);
     };
@@ -106,7 +106,7 @@ __device__ __forceinline__ void ws_issuer(const Params& p, WsSmem& sm, const Dir
 #pragma unroll
         for (int ks = 0; ks < 4; ks++) umma(tY, dk_rst + DOFF(ks * 32), dm_sp + DOFF(ks * 2048), ID_G3, ks > 0);
 #pragma unroll
-        for (int ks = 0; ks < 4; ks++) umma(tD, dm_kt + DOFF(ktbase<REV>(4) + ks * 2048), dm_v + DOFF(ks * 2048), ID_G2, ks > 0);
+        for (int ks = 0; ks < 4; ks++) umma(tD, dm_kt + DOFF(ktbase(REV, 4) + ks * 2048), dm_v + DOFF(ks * 2048), ID_G2, ks > 0);
         umma_commit(&sm.bar_s);
     };
 
@@ -177,7 +177,7 @@ __device__ __forceinline__ void ws_compute(const Params& p, WsSmem& sm, const Di
         const int row = REV ? 63 - pos : pos;
         offs[r] = sw_chunk(row, c0 >> 3) + (c0 & 7) * 2;
     }
-    const int vb_own = I == 0 ? ktbase<REV>(0) : I == 1 ? ktbase<REV>(1) : I == 2 ? ktbase<REV>(2) : ktbase<REV>(3);
+    const int vb_own = I == 0 ? ktbase(REV, 0) : I == 1 ? ktbase(REV, 1) : I == 2 ? ktbase(REV, 2) : ktbase(REV, 3);
     const uint2 u2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(D.u) + (h * N + c0) * 2);
 
     const uint32_t rawr_u32 = smem_u32(sm.raw_r), rawk_u32 = smem_u32(sm.raw_k), raww_u32 = smem_u32(sm.raw_w);
@@ -294,10 +294,10 @@ __device__ __forceinline__ void ws_compute(const Params& p, WsSmem& sm, const Di
     auto phase2 = [&](const int c) {
         const float* bt = &sm.blocktot[c & 1][0][0];
         switch (I) {   // warp-uniform
-            case 0: lean_phase2<0, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 1: lean_phase2<1, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 2: lean_phase2<2, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            default: lean_phase2<3, REV>(rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 0: lean_phase2<0>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 1: lean_phase2<1>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 2: lean_phase2<2>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            default: lean_phase2<3>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
         }
         fnext[0] = ex2(-((bt[frow] + bt[N + frow]) + (bt[2 * N + frow] + bt[3 * N + frow])));
         fnext[1] = ex2(-((bt[frow + 8] + bt[N + frow + 8]) + (bt[2 * N + frow + 8] + bt[3 * N + frow + 8])));

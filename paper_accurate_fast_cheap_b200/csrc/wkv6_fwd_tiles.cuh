@@ -26,15 +26,14 @@ __device__ __forceinline__ void sts64(uint32_t saddr, uint32_t a, uint32_t b) {
 constexpr float kLog2Log2e = 0.5287663729448977f;   // log2(log2(e)):  2^(w log2e + this) = e^w log2e
 
 // Ktil variant bases inside LeanSmem::kt (virtual row 0 of variant I), per direction
-template <bool REV>
-__device__ __forceinline__ constexpr int ktbase(int I) {
+__device__ __forceinline__ constexpr int ktbase(bool REV, int I) {
     return REV ? (I == 0 ? 20 * 1024 : I == 1 ? 18 * 1024 : I == 2 ? 14 * 1024 : I == 3 ? 0 : 8 * 1024)
                : (I == 0 ? 0 : I == 1 ? 2 * 1024 : I == 2 ? 6 * 1024 : I == 3 ? 12 * 1024 : 20 * 1024);
 }
 
 // phase 2 of one thread: cross-block factors -> Rst and the Ktil variants I+1..4 of this thread's 4 rows x 4 channels
-template <int I, bool REV>
-__device__ __forceinline__ void lean_phase2(uint32_t rst_u32, uint32_t kt_u32, const float* bt, int c0, const int (&offs)[4],
+template <int I>
+__device__ __forceinline__ void lean_phase2(const bool REV, uint32_t rst_u32, uint32_t kt_u32, const float* bt, int c0, const int (&offs)[4],
                                             const uint32_t (&ro2)[4][2], const uint32_t (&ko2)[4][2]) {
     float tot[4][4];
 #pragma unroll
@@ -68,7 +67,7 @@ __device__ __forceinline__ void lean_phase2(uint32_t rst_u32, uint32_t kt_u32, c
             f[e] = ex2(-acc[e]);                // 2^(a_{m+1} - a_I)
         }
         const uint32_t f0 = pack_bf16(f[0], f[1]), f1 = pack_bf16(f[2], f[3]);
-        const uint32_t base = kt_u32 + ktbase<REV>(m + 1);
+        const uint32_t base = kt_u32 + ktbase(REV, m + 1);
 #pragma unroll
         for (int r = 0; r < 4; r++) sts64(base + offs[r], bmul2(ko2[r][0], f0), bmul2(ko2[r][1], f1));
     }

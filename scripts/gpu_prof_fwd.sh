@@ -1,4 +1,4 @@
-# ncu full capture of two launches of the default forward chunk kernel inside the bench workload
+# ncu full capture of two launches of the forward chunk kernel (variant chosen by the environment) inside the bench workload
 set -x
 mkdir -p gpurun_out
 CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-train"
