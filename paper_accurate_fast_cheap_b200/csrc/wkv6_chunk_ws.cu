@@ -46,9 +46,8 @@ __device__ __forceinline__ void bar_sync_compute() { asm volatile("bar.sync 1, 2
 // ---------------------------------------------------------------------------------------------------------------
 // issuer warp (warp 8): one elected lane runs the whole loop
 // ---------------------------------------------------------------------------------------------------------------
-template <bool REV>
 __device__ __forceinline__ void ws_issuer(const Params& p, WsSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
-                                          const uint32_t tbase) {
+                                          const uint32_t tbase, const bool REV) {
     const int nchunks = (p.T + CL - 1) / CL;
     const uint32_t tP = tbase, tY = tbase + 64, tD = tbase + 128;
     const uint32_t rst_u32 = smem_u32(sm.rst), kt_u32 = smem_u32(sm.kt), roff_u32 = smem_u32(sm.roff);
@@ -154,9 +153,9 @@ __device__ __forceinline__ void ws_issuer(const Params& p, WsSmem& sm, const Dir
 // ---------------------------------------------------------------------------------------------------------------
 // compute warps (0-7)
 // ---------------------------------------------------------------------------------------------------------------
-template <bool REV>
 __device__ __forceinline__ void ws_compute(const Params& p, WsSmem& sm, const DirArgs& D, const int h, const int bh,
-                                           const int warp, const uint32_t tbase, float (&st)[16], const uint32_t (&stoff)[2]) {
+                                           const int warp, const uint32_t tbase, float (&st)[16], const uint32_t (&stoff)[2],
+                                           const bool REV) {
     const int tid = threadIdx.x, lane = tid & 31;
     const int T = p.T;
     const int nchunks = (T + CL - 1) / CL;
@@ -414,8 +413,9 @@ __device__ __forceinline__ void ws_compute(const Params& p, WsSmem& sm, const Di
     }
 }
 
-template <bool REV>
-__device__ __forceinline__ void ws_body(const Params& p, WsSmem& sm, const DirArgs& D, const int b, const int h, const int bh) {
+// REV is a runtime flag (one instantiation), see wkv6_chunk_lean.cu
+__device__ __forceinline__ void ws_body(const Params& p, WsSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
+                                        const bool REV) {
     const int tid = threadIdx.x, lane = tid & 31;
     // warp index through a lane-0 broadcast: everything derived from it stays in uniform registers
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -478,11 +478,11 @@ __device__ __forceinline__ void ws_body(const Params& p, WsSmem& sm, const DirAr
     const uint32_t tbase = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
 
     if (warp == 8) {
-        if (elect_one()) ws_issuer<REV>(p, sm, D, b, h, bh, tbase);
+        if (elect_one()) ws_issuer(p, sm, D, b, h, bh, tbase, REV);
         __syncwarp();
     } else {
         mbar_arrive(&sm.bar_sp);   // phase 0: the initial state is in sp
-        ws_compute<REV>(p, sm, D, h, bh, warp, tbase, st, stoff);
+        ws_compute(p, sm, D, h, bh, warp, tbase, st, stoff, REV);
         if (D.sT) {
             float* sT = D.sT + (size_t)bh * N * N;
 #pragma unroll
@@ -519,8 +519,7 @@ __global__ void __launch_bounds__(288, 2) wkv6_fwd_chunk_ws_kernel(const __grid_
         p.dbg[128 + 4 * blockIdx.x] = t;
         p.dbg[129 + 4 * blockIdx.x] = smid;
     }
-    if (D.reverse) ws_body<true>(p, sm, D, b, h, bh);
-    else ws_body<false>(p, sm, D, b, h, bh);
+    ws_body(p, sm, D, b, h, bh, D.reverse != 0);
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
