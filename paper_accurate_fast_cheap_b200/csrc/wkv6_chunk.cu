@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_kernel(const __grid_con
     Chunk256Smem& sm = *reinterpret_cast<Chunk256Smem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     const int BH = p.B * p.H;
     const int ds = blockIdx.x / BH;
     const int bh = blockIdx.x - ds * BH;

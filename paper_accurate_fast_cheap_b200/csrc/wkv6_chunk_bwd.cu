@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     BwdChunkSmem& sm = *reinterpret_cast<BwdChunkSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
 
     const int tid = threadIdx.x, lane = tid & 31;
+    const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     // warp index through a lane-0 broadcast: keeps MMA operands / role branches in uniform registers (a plain tid >> 5
     // turns every UTCHMMA into a waterfall loop of R2UR broadcasts)
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);

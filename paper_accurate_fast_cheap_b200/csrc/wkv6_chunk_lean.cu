@@ -42,6 +42,7 @@ struct LeanSmem {
 __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
                                           const bool REV) {
     const int tid = threadIdx.x, lane = tid & 31;
+    const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     // warp index through a lane-0 broadcast: the compiler then keeps it (and everything derived from it: MMA operands,
     // descriptors, role branches) in uniform registers; a plain tid >> 5 makes every UTCHMMA a waterfall loop
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);

@@ -157,6 +157,7 @@ __device__ __forceinline__ void ws_compute(const Params& p, WsSmem& sm, const Di
                                            const int warp, const uint32_t tbase, float (&st)[16], const uint32_t (&stoff)[2],
                                            const bool REV) {
     const int tid = threadIdx.x, lane = tid & 31;
+    const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     const int T = p.T;
     const int nchunks = (T + CL - 1) / CL;
     const uint32_t tP = tbase, tY = tbase + 64, tD = tbase + 128;
@@ -417,6 +418,7 @@ __device__ __forceinline__ void ws_compute(const Params& p, WsSmem& sm, const Di
 __device__ __forceinline__ void ws_body(const Params& p, WsSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
                                         const bool REV) {
     const int tid = threadIdx.x, lane = tid & 31;
+    const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     // warp index through a lane-0 broadcast: everything derived from it stays in uniform registers
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
 
