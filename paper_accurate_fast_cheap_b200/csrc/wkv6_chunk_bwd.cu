@@ -56,7 +56,7 @@ struct BwdChunkSmem {
     float bonus[2][CL];                      // sum_j r u k per row (two channel halves)
     float vg[CL];                            // v_p . gy_p per row
     float gured[8][N / 2];
-    alignas(8) uint64_t bar_rkw, bar_vg[2], bar_sp, bar_m1, bar_mp, bar_m2;
+    alignas(8) uint64_t bar_rkw, bar_vg[2], bar_sp, bar_m1, bar_mp, bar_m2, bar_m2b;
     uint32_t tmem_base;
 };
 static_assert(sizeof(BwdChunkSmem) <= 226 * 1024, "shared memory budget");
@@ -99,7 +99,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         mbar_init(&sm.bar_sp, 1);
         mbar_init(&sm.bar_mp, 4);     // MMA groups are issued by several warps' lane 0 in parallel (an issue costs
         mbar_init(&sm.bar_m1, 3);     // ~50 cycles of dependent uniform-datapath work); every issuer commits
-        mbar_init(&sm.bar_m2, 6);
+        mbar_init(&sm.bar_m2, 4);       // R^T / K^T groups: four issuing lanes
+        mbar_init(&sm.bar_m2b, 2);      // GV, dC
         fence_barrier_init();
         tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
         tma_prefetch_desc(&D.mg); tma_prefetch_desc(&D.mc);
@@ -453,42 +454,45 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         __syncthreads();   // B3: masked tiles complete
         WKV6_TS(64, 9);
 
-        // ================= MMA phase 2: six issuing lanes (warps 0-3: R^T and K^T group w; warp 4: GV; warp 5: dC)
-        if (warp < 6 && elect_one()) {
+        // ================= MMA phase 2: four issuing lanes.  Warp w issues the R^T and K^T groups w (10 MMAs) and commits
+        // them to bar_m2; warps 0 / 1 then add GV / dC (8 MMAs each, bar_m2b): in the tensor-pipe queue those come after
+        // the R^T / K^T groups, whose drain (the long part of E2) then overlaps them.
+        if (warp < 4 && elect_one()) {
             tc_fence_after();
-            if (warp < 4) {
-                {   // R^T[j][p in sub-block i] = sum over q in sub-blocks <= i
-                    const int i = warp;
-                    const int rb = rev ? 3 - i : i;
-                    const int vbi = i == 0 ? vbK[0] : i == 1 ? vbK[1] : i == 2 ? vbK[2] : vbK[3];
-                    for (int s_ = 0; s_ <= i; s_++) {
-                        const int kb = rev ? 3 - s_ : s_;
-                        umma(tR + 16 * rb, dm_kt + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > 0);
-                        umma(tR + 16 * rb, dm_ktl + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
-                    }
+            {   // R^T[j][p in sub-block i] = sum over q in sub-blocks <= i
+                const int i = warp;
+                const int rb = rev ? 3 - i : i;
+                const int vbi = i == 0 ? vbK[0] : i == 1 ? vbK[1] : i == 2 ? vbK[2] : vbK[3];
+                for (int s_ = 0; s_ <= i; s_++) {
+                    const int kb = rev ? 3 - s_ : s_;
+                    umma(tR + 16 * rb, dm_kt + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > 0);
+                    umma(tR + 16 * rb, dm_ktl + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
                 }
-                {   // K^T[j][q in sub-block j] = sum over p in sub-blocks >= j
-                    const int j = warp;
-                    const int rb = rev ? 3 - j : j;
-                    const int vbj = j == 0 ? vbR[0] : j == 1 ? vbR[1] : j == 2 ? vbR[2] : vbR[3];
-                    for (int s_ = j; s_ < 4; s_++) {
-                        const int kb = rev ? 3 - s_ : s_;
-                        umma(tK + 16 * rb, dm_rp + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > j);
-                        umma(tK + 16 * rb, dm_rpl + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
-                    }
+            }
+            {   // K^T[j][q in sub-block j] = sum over p in sub-blocks >= j
+                const int j = warp;
+                const int rb = rev ? 3 - j : j;
+                const int vbj = j == 0 ? vbR[0] : j == 1 ? vbR[1] : j == 2 ? vbR[2] : vbR[3];
+                for (int s_ = j; s_ < 4; s_++) {
+                    const int kb = rev ? 3 - s_ : s_;
+                    umma(tK + 16 * rb, dm_rp + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > j);
+                    umma(tK + 16 * rb, dm_rpl + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
                 }
-            } else if (warp == 4) {
+            }
+            umma_commit(&sm.bar_m2);
+            if (warp == 0) {
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++) umma(tGV, dk_pt + DOFF(ks * 32), dm_g + DOFF(ks * 2048), ID_KM64, ks > 0);
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++) umma(tGV, dk_kend + DOFF(ks * 32), dm_cp + DOFF(ks * 2048), ID_KM64, 1);
-            } else {
+                umma_commit(&sm.bar_m2b);
+            } else if (warp == 1) {
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++) umma(tDC, dm_rst + DOFF(ks * 2048), dm_g + DOFF(ks * 2048), ID_MM64, ks > 0);
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++) umma(tDC, dm_rstl + DOFF(ks * 2048), dm_g + DOFF(ks * 2048), ID_MM64, 1);
+                umma_commit(&sm.bar_m2b);
             }
-            umma_commit(&sm.bar_m2);
         }
         __syncwarp();
 
@@ -547,6 +551,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                         xk[qq * XSTR + jj] = fmaf(sK[hh][rep >> 1], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
                     }
             // gv tile [q][i]
+            mbar_wait(&sm.bar_m2b, par);
+            tc_fence_after();
             tmem_ld_16x32(tGV + lane_field + 32 * half, x);
 #pragma unroll
             for (int rep = 0; rep < 4; rep++)
