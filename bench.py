@@ -284,16 +284,22 @@ def run_b200(args):
     fwd_bytes = 2 * 5 * B * T * C * 2                     # both directions: read r,k,v,w + write y, bf16
     bwd_bytes = 2 * 9 * B * T * C * 2                     # read r,k,v,w,gy + write gr,gk,gv,gw
 
-    def roof(kernel, nbytes, ms):
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
+    # (profiles/r1_chunk_kernels_ncu_summary.txt): fwd 98.5 + 19.0 MB, bwd 148.3 + 62.4 MB (outputs partly still in L2)
+    NCU_TRAFFIC = {"fwd": 117.49e6, "bwd": 210.71e6}
+
+    def roof(kernel, nbytes, ms, traffic=None):
         ach = nbytes / (ms * 1e-3) / 1e9
         return {"bound": "hbm", "kernel": kernel, "achieved": ach, "peak": pk_["hbm_gbs"], "unit": "GB/s",
-                "frac": ach / pk_["hbm_gbs"], "peak_source": how, "traffic": None, "alg_bytes_per_launch": nbytes,
+                "frac": ach / pk_["hbm_gbs"], "peak_source": how, "traffic": traffic, "alg_bytes_per_launch": nbytes,
                 "kernel_ms": ms}
 
-    roofline = roof("wkv6_fwd_chunk_lean_kernel: bidirectional forward, one launch per block", fwd_bytes, fwd_ms)
+    roofline = roof("wkv6_fwd_chunk_lean_kernel: bidirectional forward, one launch per block", fwd_bytes, fwd_ms,
+                    NCU_TRAFFIC["fwd"])
     extra = {}
     if train:
-        roofline = roof("wkv6_bwd_chunk_kernel: bidirectional backward, one launch per block", bwd_bytes, bwd_ms)
+        roofline = roof("wkv6_bwd_chunk_kernel: bidirectional backward, one launch per block", bwd_bytes, bwd_ms,
+                        NCU_TRAFFIC["bwd"])
         extra["roofline_fwd"] = roof("wkv6_fwd_chunk_lean_kernel (+ checkpoint stores)", fwd_bytes, fwd_ms)
         extra["roofline_fwd_bwd"] = roof("forward + backward launches of one block", fwd_bytes + bwd_bytes, fwd_ms + bwd_ms)
     elif not args.no_train:
@@ -302,7 +308,7 @@ def run_b200(args):
         tms, tf, tb, _ = timed(True, tsteps, 3)
         extra["train"] = {"metric": "encoder frames/s (bi-WKV6 fwd+bwd)", "value": world * B * T / (tms * 1e-3),
                           "unit": "frames/s", "ms_per_step": tms, "steps": tsteps,
-                          "roofline_bwd": roof("wkv6_bwd_chunk_kernel", bwd_bytes, tb),
+                          "roofline_bwd": roof("wkv6_bwd_chunk_kernel", bwd_bytes, tb, NCU_TRAFFIC["bwd"]),
                           "roofline_fwd_bwd": roof("forward + backward launches of one block", fwd_bytes + bwd_bytes, tf + tb)}
 
     # ---- end to end: pinned host inputs -> H2D -> op -> D2H of y, every step, through the C ABI
