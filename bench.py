@@ -126,6 +126,8 @@ def run_reference(args):
         return
     import oracle
     oracle.build()
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the reference arm uses every host core it can, as at N=1
+    oracle.set_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     train = args.mode == "train"
     steps = min(args.steps, 20)          # one step = one full pass on the CPU (~0.25 s fwd); bounded to a few minutes
     warm = min(args.warmup, 2)
@@ -364,6 +366,8 @@ def run_b200(args):
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
+            import oracle
+            oracle.set_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
             fps, secs, th, n = cpu_baseline_bounded(10.0, train)
             cpu = {"value": fps, "unit": "frames/s", "cores": th, "kind": "port",
                    "sample": f"{n} full passes of the workload (12 blocks x both directions x B=16 x T=750, fp32"
