@@ -25,7 +25,7 @@
 //   phase 2:  R^T[j][p in I] = Ktil(I)^T Qm^T (4 x N16);  K^T[j][q in J] = Rtil'(J)^T Qm (4 x N16);
 //             GV[q][i] = P^T G + Kend C^T;  dC^T[j][i] = Rst^T G
 // 8 accumulators x 64 columns = all 512 TMEM columns -> one CTA (256 threads) per SM.
-#include "wkv6_umma.cuh"
+#include "wkv6_fwd_tiles.cuh"
 
 namespace wkv6 {
 
@@ -118,6 +118,19 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     const int frow = 16 * qtr + (lane >> 2);
     const int fcol = 32 * half + 2 * (lane & 3);
     const uint32_t lane_field = (uint32_t)(qtr * 32) << 16;
+    // stmatrix row addresses of this lane for a 16x32 fragment (two x4 stores; matrix k = lane>>3 of store s is
+    // rep = 2s + (k>>1), hh = k&1): stoff = the fragment as it is, ttoff = its transpose (rows = fragment columns)
+    uint32_t stoff[2], ttoff[2];
+    {
+        const int k = lane >> 3, r8 = lane & 7;
+        const int row = 16 * qtr + 8 * (k & 1) + r8;
+        stoff[0] = (uint32_t)sw_chunk(row, 4 * half + (k >> 1));
+        stoff[1] = (uint32_t)sw_chunk(row, 4 * half + 2 + (k >> 1));
+        ttoff[0] = (uint32_t)sw_chunk(32 * half + 8 * (k >> 1) + r8, 2 * qtr + (k & 1));
+        ttoff[1] = (uint32_t)sw_chunk(32 * half + 16 + 8 * (k >> 1) + r8, 2 * qtr + (k & 1));
+    }
+    const int sgn = rev ? -1 : 1;
+    const int dfrag = sgn * ((lane >> 2) - 2 * (lane & 3));   // sgn * (row - column) of fragment element (rep 0, hh 0, e 0)
 
     // ---- row-major coordinates (preprocessing / final epilogue): sub-block I (direction order), 4 rows x 4 channels
     const int I = warp & 3, ch = warp >> 2;
@@ -408,45 +421,80 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         WKV6_TS(64, 6);
         tc_fence_after();
         {
+            // The causal mask is resolved per 16x16 block (warp-uniform: keep / zero / diagonal); the masked fragment goes
+            // to the tiles with stmatrix (Q^T with the transposing form) instead of per-element stores.
             float x[16];
-            tmem_ld_16x32(tQ + lane_field + 32 * half, x);
+            uint32_t pk[8];
+            tmem_ld_16x32(tQ + lane_field + 32 * half, x);   // Q[p][q]: rows p (block qtr), columns q; keep q before p
 #pragma unroll
-            for (int rep = 0; rep < 4; rep++)
+            for (int cb = 0; cb < 2; cb++) {
+                const int cls = sgn * (qtr - (2 * half + cb));
+                if (cls > 0) {
 #pragma unroll
-                for (int hh = 0; hh < 2; hh++) {
-                    const int pp = frow + 8 * hh;
-                    float y[2];
+                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = pack_bf16(x[8 * cb + 2 * i], x[8 * cb + 2 * i + 1]);
+                } else if (cls < 0) {
 #pragma unroll
-                    for (int e = 0; e < 2; e++) {
-                        const int qq = fcol + 8 * rep + e;
-                        const bool before = rev ? (qq > pp) : (qq < pp);
-                        const float val = x[4 * rep + 2 * hh + e];
-                        y[e] = before ? val : 0.f;
-                        if (qq == pp) sm.vg[pp] = val;
-                        *reinterpret_cast<__nv_bfloat16*>(sm.qmt + sw_chunk(qq, pp >> 3) + (pp & 7) * 2) = __float2bfloat16_rn(y[e]);
-                    }
-                    const int qc = fcol + 8 * rep;
-                    *reinterpret_cast<uint32_t*>(sm.qm + sw_chunk(pp, qc >> 3) + (qc & 7) * 2) = pack_bf16(y[0], y[1]);
+                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = 0u;
+                } else {
+#pragma unroll
+                    for (int rl = 0; rl < 2; rl++)
+#pragma unroll
+                        for (int hh = 0; hh < 2; hh++) {
+                            float y[2];
+#pragma unroll
+                            for (int e = 0; e < 2; e++) {
+                                const int d = dfrag + sgn * (8 * hh - 8 * rl - e);   // sgn * (p - q)
+                                const float xv = x[4 * (2 * cb + rl) + 2 * hh + e];
+                                y[e] = d > 0 ? xv : 0.f;
+                                if (d == 0) sm.vg[frow + 8 * hh] = xv;
+                            }
+                            pk[2 * (2 * cb + rl) + hh] = pack_bf16(y[0], y[1]);
+                        }
                 }
+            }
+            {
+                const uint32_t qm_u32 = smem_u32(sm.qm), qmt_u32 = smem_u32(sm.qmt);
+                stsm_x4(qm_u32 + stoff[0], pk[0], pk[1], pk[2], pk[3]);
+                stsm_x4(qm_u32 + stoff[1], pk[4], pk[5], pk[6], pk[7]);
+                stsm_x4_trans(qmt_u32 + ttoff[0], pk[0], pk[1], pk[2], pk[3]);
+                stsm_x4_trans(qmt_u32 + ttoff[1], pk[4], pk[5], pk[6], pk[7]);
+            }
             mbar_wait(&sm.bar_mp, par);
             WKV6_TS(64, 7);
             tc_fence_after();
-            tmem_ld_16x32(tP + lane_field + 32 * half, x);
+            tmem_ld_16x32(tP + lane_field + 32 * half, x);   // P^T[q][p]: rows q (block qtr), columns p; keep q before p
 #pragma unroll
-            for (int rep = 0; rep < 4; rep++)
+            for (int cb = 0; cb < 2; cb++) {
+                const int cls = sgn * ((2 * half + cb) - qtr);
+                if (cls > 0) {
 #pragma unroll
-                for (int hh = 0; hh < 2; hh++) {
-                    const int qq = frow + 8 * hh;
-                    float y[2];
+                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = pack_bf16(x[8 * cb + 2 * i], x[8 * cb + 2 * i + 1]);
+                } else if (cls < 0) {
 #pragma unroll
-                    for (int e = 0; e < 2; e++) {
-                        const int pp = fcol + 8 * rep + e;
-                        const bool before = rev ? (qq > pp) : (qq < pp);
-                        y[e] = before ? x[4 * rep + 2 * hh + e] : (qq == pp ? sm.bonus[0][pp] + sm.bonus[1][pp] : 0.f);
-                    }
-                    const int pc = fcol + 8 * rep;
-                    *reinterpret_cast<uint32_t*>(sm.pt + sw_chunk(qq, pc >> 3) + (pc & 7) * 2) = pack_bf16(y[0], y[1]);
+                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = 0u;
+                } else {
+                    float bon[2];
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) bon[hh] = sm.bonus[0][frow + 8 * hh] + sm.bonus[1][frow + 8 * hh];
+#pragma unroll
+                    for (int rl = 0; rl < 2; rl++)
+#pragma unroll
+                        for (int hh = 0; hh < 2; hh++) {
+                            float y[2];
+#pragma unroll
+                            for (int e = 0; e < 2; e++) {
+                                const int d = -dfrag + sgn * (8 * rl + e - 8 * hh);   // sgn * (p - q)
+                                y[e] = d > 0 ? x[4 * (2 * cb + rl) + 2 * hh + e] : (d == 0 ? bon[hh] : 0.f);
+                            }
+                            pk[2 * (2 * cb + rl) + hh] = pack_bf16(y[0], y[1]);
+                        }
                 }
+            }
+            {
+                const uint32_t pt_u32 = smem_u32(sm.pt);
+                stsm_x4(pt_u32 + stoff[0], pk[0], pk[1], pk[2], pk[3]);
+                stsm_x4(pt_u32 + stoff[1], pk[4], pk[5], pk[6], pk[7]);
+            }
         }
         fence_proxy_async();
         tc_fence_before();

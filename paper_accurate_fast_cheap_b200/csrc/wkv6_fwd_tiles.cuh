@@ -19,6 +19,11 @@ __device__ __forceinline__ void stsm_x4(uint32_t saddr, uint32_t a, uint32_t b, 
     asm volatile("stmatrix.sync.aligned.m8n8.x4.shared.b16 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d)
                  : "memory");
 }
+// transposed store: memory row r of matrix k (address from lane 8k + r) receives COLUMN r of the fragment matrix
+__device__ __forceinline__ void stsm_x4_trans(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("stmatrix.sync.aligned.m8n8.x4.trans.shared.b16 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d)
+                 : "memory");
+}
 __device__ __forceinline__ void sts64(uint32_t saddr, uint32_t a, uint32_t b) {
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(saddr), "r"(a), "r"(b) : "memory");
 }
