@@ -369,8 +369,11 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     if (m >= I) {               // target variant I' = m + 1 (I' = 4 -> Kend)
 #pragma unroll
                         for (int e = 0; e < 4; e++) x4[e] = ko[e] * fk[m][e];
+                        // low-order halves only where the gw cancellation needs them: variant I' = I + 1 (and the own
+                        // variant, phase 1); farther variants are damped by at least one whole sub-block of decay
                         if (m == 3) st4bf(kend + off, x4);
-                        else st4bf_hilo(sm.kt + vbK[m + 1] + off, sm.kt_lo + vbK[m + 1] + off, x4);
+                        else if (m == I) st4bf_hilo(sm.kt + vbK[m + 1] + off, sm.kt_lo + vbK[m + 1] + off, x4);
+                        else st4bf(sm.kt + vbK[m + 1] + off, x4);
                     }
                 }
             }
@@ -409,7 +412,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     if (J <= I) {
 #pragma unroll
                         for (int e = 0; e < 4; e++) x4[e] = ro[e] * fr[J][e];
-                        st4bf_hilo(sm.rp + vbR[J] + off, sm.rp_lo + vbR[J] + off, x4);
+                        if (J + 1 >= I) st4bf_hilo(sm.rp + vbR[J] + off, sm.rp_lo + vbR[J] + off, x4);   // own / previous sub-block
+                        else st4bf(sm.rp + vbR[J] + off, x4);
                     }
                 }
             }
@@ -514,7 +518,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 for (int s_ = 0; s_ <= i; s_++) {
                     const int kb = rev ? 3 - s_ : s_;
                     umma(tR + 16 * rb, dm_kt + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > 0);
-                    umma(tR + 16 * rb, dm_ktl + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
+                    if (s_ + 1 >= i)   // low-order halves exist for the diagonal and the adjacent sub-block only
+                        umma(tR + 16 * rb, dm_ktl + DOFF(vbi + kb * 2048), dk_qm + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
                 }
             }
             {   // K^T[j][q in sub-block j] = sum over p in sub-blocks >= j
@@ -524,7 +529,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 for (int s_ = j; s_ < 4; s_++) {
                     const int kb = rev ? 3 - s_ : s_;
                     umma(tK + 16 * rb, dm_rp + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, s_ > j);
-                    umma(tK + 16 * rb, dm_rpl + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
+                    if (s_ <= j + 1)
+                        umma(tK + 16 * rb, dm_rpl + DOFF(vbj + kb * 2048), dk_qmt + DOFF(rb * 2048 + kb * 32), ID_MK16, 1);
                 }
             }
             umma_commit(&sm.bar_m2);
