@@ -18,6 +18,8 @@ static std::atomic<int> g_algo{WKV6_ALGO_AUTO};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 static unsigned long long* g_dbg = nullptr;
+static void* g_scratch = nullptr;          // device scratch lent by the caller (wkv6_b200_set_scratch); never owned
+static size_t g_scratch_bytes = 0;
 unsigned long long* debug_trace_buffer() { return g_dbg; }
 
 static int fail(int code, const char* fmt, ...) {
@@ -169,7 +171,13 @@ static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets
     const bool chunk = use_chunk(dtype, T);
     for (int i = 0; i < nset; i++)
         if ((e = fill_fwd(p.d[i], dtype, B, T, C, sets[i], reverse[i], chunk ? 64 : TT, chunk))) return e;
-    e = chunk ? launch_fwd_chunk(p, (cudaStream_t)stream) : launch_fwd_scan(dtype, p, (cudaStream_t)stream);
+    if (chunk) {
+        // long sequences with few (batch, head) pairs: time-segmented two-pass forward on the lent scratch buffer
+        e = launch_fwd_chunk_segmented(p, g_scratch, g_scratch_bytes, (cudaStream_t)stream);
+        if (e < 0) e = launch_fwd_chunk(p, (cudaStream_t)stream);
+    } else {
+        e = launch_fwd_scan(dtype, p, (cudaStream_t)stream);
+    }
     return cuda_fail(e, "wkv6 forward launch");
 }
 
@@ -293,6 +301,14 @@ int wkv6_b200_debug_trace(int enable, unsigned long long* out) {
     }
     if (out && g_dbg) cudaMemcpy(out, g_dbg, 128 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     if (!enable && g_dbg) { cudaFree(g_dbg); g_dbg = nullptr; }
+    return 0;
+}
+/* Lend (or, with NULL / 0, take back) a device scratch buffer for the time-segmented forward of long sequences.  The
+ * library never allocates or frees it; it is used by forward calls on whatever stream they run (one stream at a time). */
+int wkv6_b200_set_scratch(void* device_ptr, size_t bytes) {
+    if (device_ptr && !aligned16(device_ptr)) return fail(WKV6_E_BADARG, "set_scratch: misaligned pointer");
+    g_scratch = device_ptr;
+    g_scratch_bytes = device_ptr ? bytes : 0;
     return 0;
 }
 int wkv6_b200_debug_trace_ctas(unsigned long long* out) {

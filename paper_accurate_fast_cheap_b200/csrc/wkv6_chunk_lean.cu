@@ -39,15 +39,20 @@ struct LeanSmem {
 
 // REV is a RUNTIME flag on purpose: with the direction as a template parameter the two instantiations of co-resident CTAs
 // thrashed the instruction cache (ncu: "no instruction" top stall; 50.8 us mixed vs 45.6 us single-direction launches)
+// The CTA processes the chunks [cbeg, cbeg + nchunks) of its sequence (processing order), starting from the state *s0p
+// (null: zero) and leaving the final state in *sTp (unless null); decay_out (unless null) receives the product of all
+// per-step decays of that range per key channel.  Unsegmented: cbeg = 0, nchunks = all.
 __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
-                                          const bool REV) {
+                                          const bool REV, const int cbeg, const int nchunks, const float* s0p, float* sTp,
+                                          float* decay_out, const bool skip_y, const bool ckpt_on) {
     const int tid = threadIdx.x, lane = tid & 31;
     const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     // warp index through a lane-0 broadcast: the compiler then keeps it (and everything derived from it: MMA operands,
     // descriptors, role branches) in uniform registers; a plain tid >> 5 makes every UTCHMMA a waterfall loop
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int T = p.T;
-    const int nchunks = (T + CL - 1) / CL;
+    const int ntot = (T + CL - 1) / CL;
+    auto tileq = [&](int c) { return REV ? ntot - 1 - (cbeg + c) : cbeg + c; };   // tile index in memory of local chunk c
     // one elected lane of warp 5 issues every TMA load / store; one elected lane of warps 0..4 issues the MMAs
 #define TMA_THR (warp == 5 && elect_one())
 
@@ -62,7 +67,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
     }
     if (TMA_THR) {
         tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
-        if (!p.skip_y) tma_prefetch_desc(&D.my);
+        if (!skip_y) tma_prefetch_desc(&D.my);
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
@@ -104,9 +109,10 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
     const uint32_t pt_u32 = smem_u32(sm.pt), ys_u32 = smem_u32(sm.ys), sp_u32 = smem_u32(sm.sp);
 
     // state S^T[j][i]: j = frow + 8*hh, i = fcol + 8*rep + e  ->  st[4*rep + 2*hh + e]
+    float dprod0 = 1.f, dprod1 = 1.f;   // product of the chunk decays 2^(A_L[j]), j = frow, frow + 8 (segmented pass 1)
     float st[16];
     {
-        const float* s0 = D.s0 ? D.s0 + (size_t)bh * N * N : nullptr;
+        const float* s0 = s0p;
 #pragma unroll
         for (int rep = 0; rep < 4; rep++)
 #pragma unroll
@@ -131,14 +137,14 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
     const uint32_t tP = tbase, tY = tbase + 64, tD = tbase + 128;
 
     auto issue_rkw = [&](int c) {   // TMA_THR only
-        const int q = REV ? nchunks - 1 - c : c;
+        const int q = tileq(c);
         mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
         tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q * CL, b);
         tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q * CL, b);
         tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q * CL, b);
     };
     auto issue_v = [&](int c) {
-        const int q = REV ? nchunks - 1 - c : c;
+        const int q = tileq(c);
         mbar_arrive_expect_tx(&sm.bar_v[c & 1], (uint32_t)CL * 128);
         tma_load_3d(sm.v[c & 1], &D.mv, &sm.bar_v[c & 1], h * N, q * CL, b);
     };
@@ -156,7 +162,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
 
     // ---- phase 1 of chunk c: decays, in-block cumulative sums, Rtil, Ktil(own block), bonus
     auto phase1 = [&](const int c) {
-        const int q = REV ? nchunks - 1 - c : c;
+        const int q = tileq(c);
         const int t0 = q * CL;
         mbar_wait(&sm.bar_rkw, c & 1);
         float m[4][4];
@@ -273,8 +279,8 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
                 umma_commit(&sm.bar_s);
             }
         }
-        if (TMA_THR && D.ckpt) {   // S at the start of chunk c (bf16, [j][i]) -> checkpoint c of this sequence
-            tma_store_2d(&D.mc, sm.sp, 0, (bh * nchunks + c) * N);
+        if (TMA_THR && ckpt_on) {   // S at the start of chunk c (bf16, [j][i]) -> checkpoint c of this sequence
+            tma_store_2d(&D.mc, sm.sp, 0, (bh * ntot + cbeg + c) * N);
             tma_store_commit();
         }
         __syncwarp();
@@ -293,7 +299,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
     }
 
     for (int c = 0; c < nchunks; c++) {
-        const int q = REV ? nchunks - 1 - c : c;
+        const int q = tileq(c);
         const int t0 = q * CL;
         const uint32_t par = c & 1;
         const bool more = c + 1 < nchunks;
@@ -366,6 +372,8 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             const float* bt = &sm.blocktot[par][0][0];
             const float f0 = ex2(-((bt[frow] + bt[N + frow]) + (bt[2 * N + frow] + bt[3 * N + frow])));
             const float f1 = ex2(-((bt[frow + 8] + bt[N + frow + 8]) + (bt[2 * N + frow + 8] + bt[3 * N + frow + 8])));
+            dprod0 *= f0;
+            dprod1 *= f1;
 #pragma unroll
             for (int rep = 0; rep < 4; rep++) {
                 st[4 * rep + 0] = fmaf(st[4 * rep + 0], f0, dv[4 * rep + 0]);
@@ -392,7 +400,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         mbar_wait(&sm.bar_y, par);
         WKV6_TS(0, 9);
         tc_fence_after();
-        if (!p.skip_y) {
+        if (!skip_y) {
             float yv[16];
             tmem_ld_16x32(tY + lane_field + 32 * half, yv);
             store_frag(ys_u32, yv);
@@ -403,7 +411,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         __syncthreads();   // B2: y tile, sp and the operand tiles of chunk c+1 complete; TMEM reads of chunk c done
         WKV6_TS(0, 11);
         if (TMA_THR) {
-            if (!p.skip_y) {
+            if (!skip_y) {
                 tma_store_3d(&D.my, sm.ys, h * N, t0, b);
                 tma_store_commit();
             }
@@ -415,8 +423,12 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
 
     __syncwarp();
     if (TMA_THR) tma_store_wait<0>();
-    if (D.sT) {
-        float* sT = D.sT + (size_t)bh * N * N;
+    if (decay_out && half == 0 && (lane & 3) == 0) {
+        decay_out[frow] = dprod0;
+        decay_out[frow + 8] = dprod1;
+    }
+    if (sTp) {
+        float* sT = sTp;
 #pragma unroll
         for (int rep = 0; rep < 4; rep++)
 #pragma unroll
@@ -437,8 +449,10 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
     // compiler: LDS/STS instead of generic LD/ST
     LeanSmem& sm = *reinterpret_cast<LeanSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
     const int BH = p.B * p.H;
-    const int ds = blockIdx.x / BH;
-    const int bh = blockIdx.x - ds * BH;
+    const int nseg = p.nseg > 0 ? p.nseg : 1;
+    const int seq = blockIdx.x / nseg, seg = blockIdx.x - seq * nseg;   // seq = direction * B*H + bh
+    const int ds = seq / BH;
+    const int bh = seq - ds * BH;
     const int b = bh / p.H, h = bh - b * p.H;
     const DirArgs& D = p.d[ds];
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
@@ -449,12 +463,89 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
         p.dbg[128 + 4 * blockIdx.x] = t;
         p.dbg[129 + 4 * blockIdx.x] = smid;
     }
-    lean_body(p, sm, D, b, h, bh, D.reverse != 0);
+    const int ntot = (p.T + CL - 1) / CL;
+    if (p.nseg <= 1) {
+        lean_body(p, sm, D, b, h, bh, D.reverse != 0, 0, ntot, D.s0 ? D.s0 + (size_t)bh * N * N : nullptr,
+                  D.sT ? D.sT + (size_t)bh * N * N : nullptr, nullptr, p.skip_y != 0, D.ckpt != nullptr);
+    } else {
+        // time-segmented: pass 1 leaves every segment's local state (from S = 0) and decay product in the scratch, a small
+        // scan kernel turns them into the segment-start states, pass 2 recomputes every segment from its start state
+        const int cbeg = seg * p.seg_chunks;
+        const int nloc = min(p.seg_chunks, ntot - cbeg);
+        float* slot = p.seg_state + ((size_t)seq * nseg + seg) * N * N;
+        if (p.seg_mode == 1)
+            lean_body(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, nullptr, slot, p.seg_decay + ((size_t)seq * nseg + seg) * N,
+                      true, false);
+        else
+            lean_body(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, slot,
+                      (seg == nseg - 1 && D.sT) ? D.sT + (size_t)bh * N * N : nullptr, nullptr, p.skip_y != 0, D.ckpt != nullptr);
+    }
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.dbg[130 + 4 * blockIdx.x] = t;
     }
+}
+
+// Segment scan: S_start[0] = S_0 (or 0), S_start[s+1][i][j] = S_start[s][i][j] * D_s[j] + dS_s[i][j]; the slots that pass 1
+// filled with dS_s are overwritten with S_start[s].  One CTA per (direction, batch, head), one state element per thread
+// and iteration: coalesced, a few microseconds.
+__global__ void __launch_bounds__(256) wkv6_seg_scan_kernel(const __grid_constant__ Params p) {
+    const int BH = p.B * p.H;
+    const int seq = blockIdx.x, ds = seq / BH, bh = seq - ds * BH;
+    const DirArgs& D = p.d[ds];
+    const float* s0 = D.s0 ? D.s0 + (size_t)bh * N * N : nullptr;
+    float* st = p.seg_state + (size_t)seq * p.nseg * N * N;
+    const float* dec = p.seg_decay + (size_t)seq * p.nseg * N;
+    for (int e = threadIdx.x; e < N * N; e += 256) {
+        const int j = e & (N - 1);
+        float cur = s0 ? s0[e] : 0.f;
+        for (int s = 0; s < p.nseg; s++) {
+            const float ds_ = st[(size_t)s * N * N + e];
+            st[(size_t)s * N * N + e] = cur;
+            cur = fmaf(cur, dec[s * N + j], ds_);
+        }
+    }
+}
+
+// Number of time segments for a launch (0 = unsegmented): only when one CTA per sequence leaves most SMs empty and the
+// sequences are long; two passes cost ~2x the work, so at least 4 segments, each at least 8 chunks long.
+static int pick_segments(const Params& p, size_t scratch_bytes, int* seg_chunks) {
+    const int nseq = p.ndir * p.B * p.H;
+    const int ntot = (p.T + CL - 1) / CL;
+    if (nseq <= 0 || nseq > 74 || ntot < 32) return 0;
+    int nseg = 296 / nseq;                       // 148 SMs x 2 resident CTAs
+    if (nseg > ntot / 8) nseg = ntot / 8;
+    if (nseg < 4) return 0;
+    int sc = (ntot + nseg - 1) / nseg;
+    nseg = (ntot + sc - 1) / sc;                 // no empty segments
+    const size_t need = (size_t)nseq * nseg * (N * N + N) * sizeof(float);
+    if (need > scratch_bytes) return 0;
+    *seg_chunks = sc;
+    return nseg;
+}
+
+int launch_fwd_chunk_lean(const Params& p, cudaStream_t st);
+
+// Segmented forward: pass 1, scan, pass 2 on the caller's scratch buffer.  Returns -1 when the launch does not qualify.
+int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    int sc = 0;
+    const int nseg = scratch ? pick_segments(p, scratch_bytes, &sc) : 0;
+    if (nseg == 0) return -1;
+    const int nseq = p.ndir * p.B * p.H;
+    Params q = p;
+    q.nseg = nseg;
+    q.seg_chunks = sc;
+    q.seg_state = static_cast<float*>(scratch);
+    q.seg_decay = q.seg_state + (size_t)nseq * nseg * N * N;
+    q.seg_mode = 1;
+    int e = launch_fwd_chunk_lean(q, st);
+    if (e) return e;
+    wkv6_seg_scan_kernel<<<dim3(nseq), dim3(256), 0, st>>>(q);
+    count_launch(1);
+    if ((e = (int)cudaGetLastError())) return e;
+    q.seg_mode = 2;
+    return launch_fwd_chunk_lean(q, st);
 }
 
 int launch_fwd_chunk_lean(const Params& p, cudaStream_t st) {
@@ -473,7 +564,7 @@ int launch_fwd_chunk_lean(const Params& p, cudaStream_t st) {
     }
     Params q = p;
     q.dbg = debug_trace_buffer();
-    wkv6_fwd_chunk_lean_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), smem, st>>>(q);
+    wkv6_fwd_chunk_lean_kernel<<<dim3(q.ndir * q.B * q.H * (q.nseg > 0 ? q.nseg : 1)), dim3(256), smem, st>>>(q);
     count_launch(1);
     return (int)cudaGetLastError();
 }

@@ -34,6 +34,11 @@ struct Params {
     int B, T, C, H;
     int ndir;
     int skip_y;                           // chunk forward: compute states/checkpoints only (backward recompute)
+    // time-segmented forward (long sequences, few (batch, head) pairs; wkv6_chunk_lean.cu): 0 = one CTA per sequence
+    int nseg, seg_chunks;                 // segments per sequence, 64-step chunks per segment
+    int seg_mode;                         // 1: pass 1 (local state + decay product of every segment), 2: pass 2 (outputs)
+    float* seg_state;                     // [ndir][B*H][nseg][64 i][64 j]: pass 1 writes dS, the scan turns it into S_start
+    float* seg_decay;                     // [ndir][B*H][nseg][64 j]: product of the per-step decays of the segment
     int dir_interleave;                   // forward ws kernel: direction = blockIdx parity instead of blockIdx / (B*H)
     unsigned long long* dbg;              // optional clock64() trace of one CTA (wkv6_b200_debug_trace), else null
 };
@@ -42,6 +47,7 @@ struct Params {
 int launch_fwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_bwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_fwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05
+int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
 int launch_bwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05; needs DirArgs::ckpt
 int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out, cudaStream_t st);
 

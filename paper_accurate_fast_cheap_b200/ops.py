@@ -46,6 +46,33 @@ def _check_inputs(r, k, v, w, u, extra=()):
     return B, T, C, H
 
 
+_SCRATCH = {}
+SCRATCH_BYTES = 6 << 20      # covers every segmented launch (<= 296 segment slots x (64*64 + 64) floats)
+
+
+def _lend_scratch(t: torch.Tensor) -> None:
+    """Long sequences with few (batch, head) pairs run time-segmented (include/wkv6_b200.h: wkv6_b200_set_scratch); the
+    library never allocates, so the host side lends it a small per-device buffer once (torch caching allocator)."""
+    if t.dtype != torch.bfloat16 or t.size(1) < 2048:
+        return
+    key = t.device.index
+    if key not in _SCRATCH:
+        _SCRATCH[key] = torch.empty(SCRATCH_BYTES, device=t.device, dtype=torch.uint8)
+    buf = _SCRATCH[key]
+    _lib.check(_lib.lib().wkv6_b200_set_scratch(buf.data_ptr(), buf.numel()))
+
+
+def set_segmentation(enabled: bool) -> None:
+    """Test / A-B switch: take the scratch buffer back so that every forward runs one CTA per sequence."""
+    global _lend_scratch_enabled
+    _lend_scratch_enabled = bool(enabled)
+    if not enabled:
+        _lib.check(_lib.lib().wkv6_b200_set_scratch(None, 0))
+
+
+_lend_scratch_enabled = True
+
+
 def _check_state(s, B, H, dev):
     if s is not None:
         assert s.dtype == torch.float32 and s.is_contiguous() and s.device == dev
@@ -69,6 +96,8 @@ def wkv6_forward_raw(r, k, v, w, u, s0=None, reverse=False, want_state=False, ck
     _check_state(s0, B, H, r.device)
     y = torch.empty_like(r)
     sT = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_state else None
+    if _lend_scratch_enabled:
+        _lend_scratch(r)
     with torch.cuda.device(r.device):
         _lib.check(_lib.lib().wkv6_b200_forward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u),
                                                 _p(s0), _p(y), _p(sT), _p(ckpt), int(bool(reverse)), _stream(r)))
@@ -114,6 +143,8 @@ def bi_forward_raw(f, b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, 
     ba = tuple(_p(t) for t in b) if run_b else none5
     ck_f = ckpt[0] if (ckpt is not None and run_f) else None
     ck_b = ckpt[1] if (ckpt is not None and run_b) else None
+    if _lend_scratch_enabled:
+        _lend_scratch(ref[0])
     with torch.cuda.device(dev):
         _lib.check(_lib.lib().wkv6_b200_bi_forward(_dtype_code(ref[0]), B, T, C, H,
                                                    *fa, _p(s0_f), _p(y_f), _p(sT_f), _p(ck_f),

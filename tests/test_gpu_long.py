@@ -96,3 +96,68 @@ def test_cfg4_training_shape_bf16_gradients():
         ref = oracle.bwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], inp["gy"], rev=rev, prec="f64")
         for name, x, y in zip(("gr", "gk", "gv", "gw", "gu"), o[:5], ref[:5]):
             assert oracle.rel_err(x, y) <= TOL[torch.bfloat16], (name, rev)
+
+
+@pytest.mark.parametrize("with_state", [False, True])
+def test_cfg3_time_segmented_forward(with_state):
+    """configs[2] at 8 GPUs: ONE utterance per GPU (B = 1, 8 heads, both directions = 16 sequences of T = 30 000).  With
+    the scratch buffer lent (ops._lend_scratch) the forward runs time-segmented (pass 1 / segment scan / pass 2: three
+    launches); y, S_T and the chunk checkpoints agree with the one-CTA-per-sequence run and with the fp64 oracle."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import ops
+    B, T, H = 1, 30000, 8
+    a = _inputs(B, T, H, torch.bfloat16, with_state=with_state, seed=33)
+    b = _inputs(B, T, H, torch.bfloat16, with_state=with_state, seed=34, layer=7)
+    ga, gb = _cuda(a), _cuda(b)
+    f, r_ = tuple(ga[n] for n in "rkvwu"), tuple(gb[n] for n in "rkvwu")
+    kw = dict(s0_f=ga.get("s0"), s0_b=gb.get("s0"), want_state=True)
+    ops.set_segmentation(False)
+    try:
+        n0 = pk.launch_count()
+        y_f0, y_b0, s_f0, s_b0 = pk.bi_forward_raw(f, r_, **kw)
+        assert pk.launch_count() - n0 == 1
+    finally:
+        ops.set_segmentation(True)
+    n0 = pk.launch_count()
+    y_f, y_b, s_f, s_b = pk.bi_forward_raw(f, r_, **kw)
+    assert pk.launch_count() - n0 == 3, "expected pass 1 + segment scan + pass 2"
+    for x, x0 in ((y_f, y_f0), (y_b, y_b0), (s_f, s_f0), (s_b, s_b0)):
+        assert oracle.rel_err(x.cpu(), x0.cpu().double()) <= 1e-2      # same tolerance class: bf16 operands, regrouped sums
+    ya, sa = oracle.fwd(a["r"], a["k"], a["v"], a["w"], a["u"], a.get("s0"), want_state=True, prec="f64")
+    yb, sb = oracle.fwd(b["r"], b["k"], b["v"], b["w"], b["u"], b.get("s0"), rev=True, want_state=True, prec="f64")
+    tol = TOL[torch.bfloat16]
+    assert oracle.rel_err(y_f, ya) <= tol and oracle.rel_err(y_b, yb) <= tol
+    assert oracle.rel_err(s_f, sa) <= tol and oracle.rel_err(s_b, sb) <= tol
+
+
+def test_time_segmented_ragged_and_speed():
+    """Ragged T (not a multiple of 64, segments of unequal length), single direction; and the point of it: the segmented
+    run must be faster than one CTA per sequence on this shape."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import ops
+    B, T, H = 1, 20011, 4
+    inp = _inputs(B, T, H, torch.bfloat16, seed=35)
+    g = _cuda(inp)
+    args = (g["r"], g["k"], g["v"], g["w"], g["u"])
+
+    def timed():
+        pk.wkv6_forward_raw(*args, reverse=True, want_state=True)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = pk.wkv6_forward_raw(*args, reverse=True, want_state=True)
+        e1.record()
+        torch.cuda.synchronize()
+        return out, e0.elapsed_time(e1)
+
+    ops.set_segmentation(False)
+    try:
+        (y0, s0_), t_plain = timed()
+    finally:
+        ops.set_segmentation(True)
+    (y1, s1_), t_seg = timed()
+    y_ref, s_ref = oracle.fwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], rev=True, want_state=True, prec="f64")
+    assert oracle.rel_err(y1, y_ref) <= TOL[torch.bfloat16] and oracle.rel_err(s1_, s_ref) <= TOL[torch.bfloat16]
+    assert oracle.rel_err(y0, y_ref) <= TOL[torch.bfloat16]
+    print(f"T={T} 4 sequences: one CTA per sequence {t_plain:.3f} ms, time-segmented {t_seg:.3f} ms")
+    assert t_seg < 0.5 * t_plain
