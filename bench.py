@@ -231,30 +231,32 @@ def run_b200(args):
         return float(t.item())
 
     def timed(train, steps, warmup, sampler=None):
-        """`steps` steps of the 12-block workload (fwd, or fwd then bwd in reverse block order); per-kernel events on
-        the launching stream for the roofline figures.  Returns ms/step (max over ranks), avg fwd-launch ms, avg
-        bwd-launch ms, launches."""
-        fev, bev = [], []
-
-        def step(record):
+        """`steps` steps of the 12-block workload (fwd, or fwd then bwd in reverse block order), the timed region
+        bracketed by CUDA events on the launching stream with nothing but the kernel launches inside (an event record
+        between two launches serialises them and costs ~2 us each).  Kernel durations for the roofline: the inference
+        step is NL identical forward launches, so the average launch duration IS region time / launches; the training
+        step mixes two kernels, so right after the timed region the same launches are timed again as two homogeneous
+        regions (all forward launches of a step, then all backward launches), `steps` times each.
+        Returns ms/step (max over ranks), avg fwd-launch ms, avg bwd-launch ms, launches in the timed region."""
+        def step():
             for l in range(NL):
-                if record:
-                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    e0.record()
                 fwd_layer(l, train)
-                if record:
-                    e1.record(); fev.append((e0, e1))
             if train:
                 for l in reversed(range(NL)):
-                    if record:
-                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                        e0.record()
                     bwd_layer(l)
-                    if record:
-                        e1.record(); bev.append((e0, e1))
+
+        def region(fn, reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(reps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / reps
 
         for _ in range(warmup):
-            step(False)
+            step()
         barrier()
         n0 = pk.launch_count()
         if sampler:
@@ -262,13 +264,16 @@ def run_b200(args):
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
         for _ in range(steps):
-            step(True)
+            step()
         t1.record()
         barrier()
         launches = pk.launch_count() - n0
+        local_ms = t0.elapsed_time(t1) / steps
         ms = allmax(t0.elapsed_time(t1)) / steps
-        fk = sum(a.elapsed_time(b) for a, b in fev) / len(fev)
-        bk = sum(a.elapsed_time(b) for a, b in bev) / len(bev) if bev else None
+        if not train:
+            return ms, local_ms / NL, None, launches
+        fk = region(lambda: [fwd_layer(l, True) for l in range(NL)], steps) / NL
+        bk = region(lambda: [bwd_layer(l) for l in reversed(range(NL))], steps) / NL
         return ms, fk, bk, launches
 
     train = args.mode == "train"

@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     uint8_t* const o_gk = sm.qmt;   // chunk rewrites them only after thread 0 has waited for the TMA stores
     uint8_t* const o_gv = sm.pt;
 
+    pdl_launch_dependents();
     if (tid == 0) {
         mbar_init(&sm.bar_rkw, 1);
         mbar_init(&sm.bar_vg[0], 1);
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     const int coff = (c0 & 7) * 2, cchunk = c0 >> 3;
     const int vbK_own = I == 0 ? vbK[0] : I == 1 ? vbK[1] : I == 2 ? vbK[2] : vbK[3];
 
+    pdl_wait();   // first global access below (see wkv6_common.cuh)
     float u4[4];
     ld4bf(reinterpret_cast<const uint8_t*>(D.u) + (h * N + c0) * 2, u4);
     float gu4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -779,9 +781,9 @@ int launch_bwd_chunk(const Params& p, cudaStream_t st) {
     if (e != cudaSuccess) return (int)e;
     Params q = p;
     q.dbg = debug_trace_buffer();
-    wkv6_bwd_chunk_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), smem, st>>>(q);
+    e = launch_pdl(wkv6_bwd_chunk_kernel, dim3(q.ndir * q.B * q.H), dim3(256), smem, st, q);
     count_launch(1);
-    return (int)cudaGetLastError();
+    return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
 }  // namespace wkv6

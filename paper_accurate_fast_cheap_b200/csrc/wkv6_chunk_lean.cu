@@ -102,6 +102,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         offs[r] = sw_chunk(row, c0 >> 3) + (c0 & 7) * 2;
     }
     const int vb_own = I == 0 ? ktbase(REV, 0) : I == 1 ? ktbase(REV, 1) : I == 2 ? ktbase(REV, 2) : ktbase(REV, 3);
+    pdl_wait();   // first global access below: the previous kernel of the stream has completed and its writes are visible
     const uint2 u2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint8_t*>(D.u) + (h * N + c0) * 2);
 
     const uint32_t rawr_u32 = smem_u32(sm.raw_r), rawk_u32 = smem_u32(sm.raw_k), raww_u32 = smem_u32(sm.raw_w);
@@ -454,6 +455,7 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
     const int ds = seq / BH;
     const int bh = seq - ds * BH;
     const int b = bh / p.H, h = bh - b * p.H;
+    pdl_launch_dependents();   // the next launch of the stream may take the SM slots this grid leaves free (it blocks in pdl_wait())
     const DirArgs& D = p.d[ds];
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
         unsigned long long t;
@@ -564,9 +566,9 @@ int launch_fwd_chunk_lean(const Params& p, cudaStream_t st) {
     }
     Params q = p;
     q.dbg = debug_trace_buffer();
-    wkv6_fwd_chunk_lean_kernel<<<dim3(q.ndir * q.B * q.H * (q.nseg > 0 ? q.nseg : 1)), dim3(256), smem, st>>>(q);
+    const cudaError_t e = launch_pdl(wkv6_fwd_chunk_lean_kernel, dim3(q.ndir * q.B * q.H * (q.nseg > 0 ? q.nseg : 1)), dim3(256), smem, st, q);
     count_launch(1);
-    return (int)cudaGetLastError();
+    return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
 }  // namespace wkv6

@@ -165,4 +165,12 @@ __device__ __forceinline__ float sum_lanes8(float x) {
     return x;
 }
 
+
+// Programmatic dependent launch (PDL): a kernel launched with launch_pdl() may become resident while the previous kernel
+// of the stream is still draining; everything before pdl_wait() (barrier init, TMEM allocation, descriptor prefetch,
+// shared-memory clears) overlaps that tail, and no global memory is touched before it.  Without the launch attribute
+// both instructions are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 }  // namespace wkv6

@@ -1,5 +1,6 @@
 // wkv6_scan.cuh -- parameter blocks shared by the kernels and the C ABI (wkv6_capi.cu).
 #pragma once
+#include <cstdlib>
 #include "wkv6_common.cuh"
 
 namespace wkv6 {
@@ -63,5 +64,24 @@ unsigned long long* debug_trace_buffer();
     do {                                                                                          \
         if (wkv6_trace_on && c_ts == WKV6_TS_CHUNK) p.dbg[(base) + (tid ? 16 : 0) + (i)] = clock64(); \
     } while (0)
+
+
+// Launch with the programmatic-stream-serialization attribute (see pdl_wait() in wkv6_common.cuh); WKV6_NO_PDL=1 turns
+// the attribute off (plain stream order) for A/B timing.
+template <typename Kernel>
+inline cudaError_t launch_pdl(Kernel kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const Params& q) {
+    static const bool on = getenv("WKV6_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = on ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, q);
+}
 
 }  // namespace wkv6
