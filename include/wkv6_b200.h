@@ -119,6 +119,16 @@ int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
 int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum,
                       float* out, void* stream);
 
+/* Elementwise part of the time-mix prologue: token shift + "maa" mixes of RWKV_Tmix_x060c.forward,
+ * wenet/rwkv_v6/src/model.py:270-289, one pass per stage instead of ~14 eager kernels, bit-exact with them.
+ *   xx = shift(x) - x,  shift = x[t-1] (reverse = 0) or x[t+1] (reverse = 1: the flip-free right-to-left block), 0 outside
+ *   stage 1 (m == NULL):  xxx = x + xx * maa_x
+ *   stage 2 (m != NULL):  xr = x + xx * (maa_r + m[0]), xk (m[1]), xv (m[2]), xw (m[3]);   m is [4][B][T][C] contiguous
+ * x and outputs [B][T][C] contiguous in `dtype`, maa_* [C] in `dtype`; C % 8 == 0; 16-byte aligned pointers. */
+int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* m, const void* maa_x, const void* maa_r,
+                       const void* maa_k, const void* maa_v, const void* maa_w, int reverse, void* xxx, void* xr, void* xk,
+                       void* xv, void* xw, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -389,4 +389,23 @@ int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float s
     return cuda_fail(launch_combine(dtype, n, a, b, scale, round_sum, out, (cudaStream_t)stream), "wkv6 combine launch");
 }
 
+int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* m, const void* maa_x, const void* maa_r,
+                       const void* maa_k, const void* maa_v, const void* maa_w, int reverse, void* xxx, void* xr, void* xk, void* xv,
+                       void* xw, void* stream) {
+    if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
+    if (B < 0 || T < 0 || C <= 0 || C % 8) return fail(WKV6_E_BADARG, "tmix_mix: bad shape B=%d T=%d C=%d (C %% 8 == 0)", B, T, C);
+    if (B == 0 || T == 0) return 0;
+    const void* maa[5] = {maa_x, maa_r, maa_k, maa_v, maa_w};
+    void* out[4] = {m ? xr : xxx, xk, xv, xw};
+    if (!x || !aligned16(x) || (m && !aligned16(m))) return fail(WKV6_E_BADARG, "tmix_mix: NULL/misaligned x or m");
+    if (!m) {
+        if (!maa_x || !xxx || !aligned16(maa_x) || !aligned16(xxx)) return fail(WKV6_E_BADARG, "tmix_mix stage 1: NULL/misaligned maa_x or xxx");
+    } else {
+        for (int i = 0; i < 4; i++)
+            if (!maa[i + 1] || !out[i] || !aligned16(maa[i + 1]) || !aligned16(out[i]))
+                return fail(WKV6_E_BADARG, "tmix_mix stage 2: NULL/misaligned maa or output %d", i);
+    }
+    return cuda_fail(launch_tmix_mix(dtype, B, T, C, x, m, maa, reverse, out, (cudaStream_t)stream), "wkv6 tmix_mix launch");
+}
+
 }  // extern "C"

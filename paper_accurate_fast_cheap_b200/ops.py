@@ -196,3 +196,26 @@ def combine(a: torch.Tensor, b: Optional[torch.Tensor], scale: float = 0.5, roun
         _lib.check(_lib.lib().wkv6_b200_combine(_dtype_code(a), a.numel(), _p(a), _p(b), float(scale), int(bool(round_sum)),
                                                 _p(out), _stream(a)))
     return out
+
+
+def tmix_mix(x: torch.Tensor, maa_x: torch.Tensor, maa_rkvw, w1: torch.Tensor, w2: torch.Tensor, reverse: bool = False):
+    """Token shift + the five `maa` mixes of RWKV_Tmix_x060c.forward (model.py:270-289) with the two elementwise
+    stages fused (one kernel each, bit-exact with the eager ops); the LoRA GEMMs in between stay library calls.
+    x [B,T,C] contiguous; maa_* [1,1,C]; w1 [C,128], w2 [4,32,C].  Returns x_r, x_k, x_v, x_w.  Inference only (no
+    autograd graph is recorded)."""
+    assert x.is_cuda and x.is_contiguous() and x.dim() == 3
+    B, T, C = x.shape
+    L, dt, st = _lib.lib(), _dtype_code(x), _stream(x)
+    flat = lambda t: t.detach().reshape(-1).contiguous()
+    mx = flat(maa_x)
+    mr, mk, mv, mw = (flat(t) for t in maa_rkvw)
+    xxx = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), None, _p(mx), None, None, None, None, int(bool(reverse)),
+                                        _p(xxx), None, None, None, None, st))
+        m = torch.tanh(xxx.view(B * T, C) @ w1.detach()).view(B * T, 4, -1).transpose(0, 1)
+        m = torch.bmm(m, w2.detach()).contiguous()                      # [4, B*T, C]
+        outs = [torch.empty_like(x) for _ in range(4)]
+        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), _p(m), None, _p(mr), _p(mk), _p(mv), _p(mw), int(bool(reverse)),
+                                        None, *[_p(o) for o in outs], st))
+    return tuple(outs)

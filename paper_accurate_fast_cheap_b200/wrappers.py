@@ -67,6 +67,14 @@ class RWKV_Tmix_x060c(nn.Module):
     def prologue(self, x: torch.Tensor, reverse: bool = False):
         """x [B,T,C] -> contiguous r, k, v, w (model.py:270-289).  `reverse`: the token shift looks at t+1."""
         B, T, C = x.size()
+        if x.is_cuda and not torch.is_grad_enabled() and x.dtype in (torch.bfloat16, torch.float32) and C % 8 == 0:
+            # inference: the elementwise stages run fused (ops.tmix_mix, bit-exact with the eager ops below)
+            xr, xk, xv, ww = ops.tmix_mix(x.contiguous(), self.time_maa_x,
+                                          (self.time_maa_r, self.time_maa_k, self.time_maa_v, self.time_maa_w),
+                                          self.time_maa_rkvw_w1, self.time_maa_rkvw_w2, reverse)
+            w = self.time_decay + torch.tanh(ww @ self.time_decay_w1) @ self.time_decay_w2
+            return (self.receptance(xr).contiguous(), self.key(xk).contiguous(), self.value(xv).contiguous(),
+                    w.contiguous())
         if reverse:
             xx = F.pad(x[:, 1:], (0, 0, 0, 1)) - x
         else:
