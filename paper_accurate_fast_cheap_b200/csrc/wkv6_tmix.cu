@@ -24,8 +24,8 @@ namespace {
 template <typename T> struct Vec;
 template <> struct Vec<__nv_bfloat16> {
     static constexpr int W = 8;   // elements per 16-byte vector
-    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&f)[8]) {
-        const uint4 q = *reinterpret_cast<const uint4*>(p);
+    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&f)[8]) { unpack(*reinterpret_cast<const uint4*>(p), f); }
+    static __device__ __forceinline__ void unpack(const uint4 q, float (&f)[8]) {
         const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
         for (int i = 0; i < 4; i++) {
@@ -42,9 +42,9 @@ template <> struct Vec<__nv_bfloat16> {
 };
 template <> struct Vec<float> {
     static constexpr int W = 4;
-    static __device__ __forceinline__ void load(const float* p, float (&f)[4]) {
-        const float4 q = *reinterpret_cast<const float4*>(p);
-        f[0] = q.x; f[1] = q.y; f[2] = q.z; f[3] = q.w;
+    static __device__ __forceinline__ void load(const float* p, float (&f)[4]) { unpack(*reinterpret_cast<const uint4*>(p), f); }
+    static __device__ __forceinline__ void unpack(const uint4 q, float (&f)[4]) {
+        f[0] = __uint_as_float(q.x); f[1] = __uint_as_float(q.y); f[2] = __uint_as_float(q.z); f[3] = __uint_as_float(q.w);
     }
     static __device__ __forceinline__ void store(float* p, const float (&f)[4]) {
         *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
@@ -91,11 +91,14 @@ __global__ void __launch_bounds__(256) wkv6_tmix_mix_kernel(const TmixArgs a) {
             Vec<T>::store(static_cast<T*>(a.out[0]) + off, o);
         } else {
             const size_t plane = (size_t)a.rows * a.C;
+            uint4 qm[4];   // the four m_c vectors are read once: streaming loads, all in flight before the first use
+#pragma unroll
+            for (int k = 0; k < 4; k++) qm[k] = __ldcs(reinterpret_cast<const uint4*>(static_cast<const T*>(a.m) + k * plane + off));
 #pragma unroll
             for (int k = 0; k < 4; k++) {
                 float mk[W], mm[W], o[W];
                 Vec<T>::load(static_cast<const T*>(a.maa[k + 1]) + c, mk);
-                Vec<T>::load(static_cast<const T*>(a.m) + k * plane + off, mm);
+                Vec<T>::unpack(qm[k], mm);
 #pragma unroll
                 for (int i = 0; i < W; i++) {
                     const float s = Vec<T>::rnd(__fadd_rn(mk[i], mm[i]));
@@ -112,9 +115,9 @@ int launch_t(const TmixArgs& a, cudaStream_t st) {
     const long long nvec = a.rows * (a.C / Vec<T>::W);
     if (nvec == 0) return 0;
     if (nvec >= (1ll << 31)) return (int)cudaErrorInvalidValue;
-    // a multiple of the SM count: 148 SMs x 8 resident CTAs of 256 threads, grid-stride beyond that
+    // up to 148 SMs x 8 resident CTAs x 4 waves of 256 threads, grid-stride beyond that
     long long blocks = (nvec + 255) / 256;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > 148 * 32) blocks = 148 * 32;
     wkv6_tmix_mix_kernel<T, STAGE2><<<dim3((unsigned)blocks), dim3(256), 0, st>>>(a);
     count_launch(1);
     return (int)cudaGetLastError();

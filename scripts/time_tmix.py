@@ -1,0 +1,75 @@
+"""Times the fused token-shift / maa-mix stages (csrc/wkv6_tmix.cu) on the bench shape (B=16, T=750, C=512, bf16, 12
+distinct blocks so that every launch reads cold data: 110 MB per stage-2 launch) against the eager torch ops they
+replace, and prints one JSON line with the algorithmic bandwidth against the measured HBM peak."""
+import ctypes
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import _torch_ref as ref
+from paper_accurate_fast_cheap_b200 import _lib, ops
+
+B, T, C, NL = 16, 750, 512, 12
+dev = torch.device("cuda:0")
+dt = torch.bfloat16
+g = torch.Generator(device=dev).manual_seed(3)
+xs = [torch.randn(B, T, C, device=dev, generator=g).to(dt) for _ in range(NL)]
+ms = [(0.3 * torch.randn(4, B, T, C, device=dev, generator=g)).to(dt) for _ in range(NL)]
+maa = [torch.rand(C, device=dev, generator=g).to(dt) for _ in range(5)]
+maa3 = [t.view(1, 1, C) for t in maa]
+out1 = [torch.empty_like(xs[0]) for _ in range(NL)]
+out2 = [[torch.empty_like(xs[0]) for _ in range(4)] for _ in range(NL)]
+L = _lib.lib()
+p = lambda t: ctypes.c_void_p(t.data_ptr())
+st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def fused1():
+    for l in range(NL):
+        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), None, p(maa[0]), None, None, None, None, 0, p(out1[l]), None, None, None, None, st))
+
+
+def fused2():
+    for l in range(NL):
+        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), p(ms[l]), None, p(maa[1]), p(maa[2]), p(maa[3]), p(maa[4]), 0, None,
+                                        *[p(o) for o in out2[l]], st))
+
+
+def eager1():
+    for l in range(NL):
+        ref.tmix_mix_stage1(xs[l], maa3[0])
+
+
+def eager2():
+    for l in range(NL):
+        ref.tmix_mix_stage2(xs[l], ms[l], maa3[1], maa3[2], maa3[3], maa3[4])
+
+
+def timed(fn, reps=20):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / (reps * NL) * 1e3      # us per launch / per block
+
+
+peak = 6449.4
+try:
+    peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    pass
+n = B * T * C * 2
+res = {}
+for name, fn, passes in (("stage1_fused", fused1, 2), ("stage1_eager", eager1, 2), ("stage2_fused", fused2, 9), ("stage2_eager", eager2, 9)):
+    us = timed(fn)
+    res[name] = {"us_per_block": us, "algorithmic_GBps": passes * n / us / 1e3, "frac_of_hbm_peak": passes * n / us / 1e3 / peak}
+print(json.dumps({"workload": "tmix token-shift + maa mixes, B=16 x T=750 x C=512 bf16, 12 distinct blocks", "hbm_peak_GBps": peak, **res}))
