@@ -121,11 +121,12 @@ int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float s
 
 /* Elementwise part of the time-mix prologue: token shift + "maa" mixes of RWKV_Tmix_x060c.forward,
  * wenet/rwkv_v6/src/model.py:270-289, one pass per stage instead of ~14 eager kernels, bit-exact with them.
- *   xx = shift(x) - x,  shift = x[t-1] (reverse = 0) or x[t+1] (reverse = 1: the flip-free right-to-left block), 0 outside
+ *   xx = shift(x) - x,  shift = x[t-1] (reverse = 0) or x[t+1] (reverse = 1: the flip-free right-to-left block); beyond the
+ *   edge of the sequence: x_edge[b] ([B][C]: streaming, the last frame of the previous piece) or 0 when x_edge == NULL
  *   stage 1 (m == NULL):  xxx = x + xx * maa_x
  *   stage 2 (m != NULL):  xr = x + xx * (maa_r + m[0]), xk (m[1]), xv (m[2]), xw (m[3]);   m is [4][B][T][C] contiguous
  * x and outputs [B][T][C] contiguous in `dtype`, maa_* [C] in `dtype`; C % 8 == 0; 16-byte aligned pointers. */
-int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* m, const void* maa_x, const void* maa_r,
+int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* x_edge, const void* m, const void* maa_x, const void* maa_r,
                        const void* maa_k, const void* maa_v, const void* maa_w, int reverse, void* xxx, void* xr, void* xk,
                        void* xv, void* xw, void* stream);
 

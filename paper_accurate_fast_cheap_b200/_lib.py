@@ -61,7 +61,7 @@ def lib() -> ctypes.CDLL:
     L.wkv6_b200_bi_backward.restype = _i
     L.wkv6_b200_combine.argtypes = [_i, _sz, _vp, _vp, ctypes.c_float, _i, _vp, _vp]
     L.wkv6_b200_combine.restype = _i
-    L.wkv6_b200_tmix_mix.argtypes = [_i] * 4 + [_vp] * 7 + [_i] + [_vp] * 6
+    L.wkv6_b200_tmix_mix.argtypes = [_i] * 4 + [_vp] * 8 + [_i] + [_vp] * 6
     L.wkv6_b200_tmix_mix.restype = _i
     _lib = L
     return L

@@ -389,7 +389,7 @@ int wkv6_b200_combine(int dtype, size_t n, const void* a, const void* b, float s
     return cuda_fail(launch_combine(dtype, n, a, b, scale, round_sum, out, (cudaStream_t)stream), "wkv6 combine launch");
 }
 
-int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* m, const void* maa_x, const void* maa_r,
+int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* x_edge, const void* m, const void* maa_x, const void* maa_r,
                        const void* maa_k, const void* maa_v, const void* maa_w, int reverse, void* xxx, void* xr, void* xk, void* xv,
                        void* xw, void* stream) {
     if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
@@ -397,7 +397,8 @@ int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void
     if (B == 0 || T == 0) return 0;
     const void* maa[5] = {maa_x, maa_r, maa_k, maa_v, maa_w};
     void* out[4] = {m ? xr : xxx, xk, xv, xw};
-    if (!x || !aligned16(x) || (m && !aligned16(m))) return fail(WKV6_E_BADARG, "tmix_mix: NULL/misaligned x or m");
+    if (!x || !aligned16(x) || (m && !aligned16(m)) || (x_edge && !aligned16(x_edge)))
+        return fail(WKV6_E_BADARG, "tmix_mix: NULL/misaligned x, x_edge or m");
     if (!m) {
         if (!maa_x || !xxx || !aligned16(maa_x) || !aligned16(xxx)) return fail(WKV6_E_BADARG, "tmix_mix stage 1: NULL/misaligned maa_x or xxx");
     } else {
@@ -405,7 +406,7 @@ int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void
             if (!maa[i + 1] || !out[i] || !aligned16(maa[i + 1]) || !aligned16(out[i]))
                 return fail(WKV6_E_BADARG, "tmix_mix stage 2: NULL/misaligned maa or output %d", i);
     }
-    return cuda_fail(launch_tmix_mix(dtype, B, T, C, x, m, maa, reverse, out, (cudaStream_t)stream), "wkv6 tmix_mix launch");
+    return cuda_fail(launch_tmix_mix(dtype, B, T, C, x, x_edge, m, maa, reverse, out, (cudaStream_t)stream), "wkv6 tmix_mix launch");
 }
 
 }  // extern "C"

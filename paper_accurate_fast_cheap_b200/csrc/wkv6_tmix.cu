@@ -1,8 +1,9 @@
 // wkv6_tmix.cu -- the elementwise part of the time-mix prologue that feeds the WKV6 scan (first step):
 // token shift and the five "maa" mixes of RWKV_Tmix_x060c.forward (reference: wenet/rwkv_v6/src/model.py:270-289),
 //
-//     xx  = shift(x) - x                    shift = x[t-1] (left-to-right block) or x[t+1] (flip-free right-to-left block),
-//                                           zero outside the sequence
+//     xx  = shift(x) - x                    shift = x[t-1] (left-to-right block) or x[t+1] (flip-free right-to-left block);
+//                                           outside the sequence: zero, or the caller's edge frame (streaming: the last
+//                                           frame of the previous piece)
 //     stage 1:  xxx = x + xx * maa_x                                            (input of the LoRA GEMM)
 //     stage 2:  x_c = x + xx * (maa_c + m_c)   for c in {r, k, v, w}            (inputs of the r / k / v / decay GEMMs)
 //
@@ -54,6 +55,7 @@ template <> struct Vec<float> {
 
 struct TmixArgs {
     const void* x;
+    const void* x_edge;   // [B][C] frame beyond the edge (x[-1], or x[T] when reverse), or null: zeros
     const void* m;        // [4][B*T*C] (r, k, v, w) or null: stage 1
     const void* maa[5];   // x, r, k, v, w: [C]
     void* out[4];         // stage 1: out[0] = xxx; stage 2: x_r, x_k, x_v, x_w
@@ -76,8 +78,12 @@ __global__ void __launch_bounds__(256) wkv6_tmix_mix_kernel(const TmixArgs a) {
         Vec<T>::load(x + off, xv);
         const bool edge = a.reverse ? (t == a.T - 1) : (t == 0);
         if (edge) {
+            if (a.x_edge) {
+                Vec<T>::load(static_cast<const T*>(a.x_edge) + (size_t)(row / (unsigned)a.T) * a.C + c, xs);
+            } else {
 #pragma unroll
-            for (int i = 0; i < W; i++) xs[i] = 0.f;
+                for (int i = 0; i < W; i++) xs[i] = 0.f;
+            }
         } else {
             Vec<T>::load(a.reverse ? x + off + a.C : x + off - a.C, xs);
         }
@@ -125,10 +131,11 @@ int launch_t(const TmixArgs& a, cudaStream_t st) {
 
 }  // namespace
 
-int launch_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* m, const void* const* maa, int reverse, void* const* out,
-                    cudaStream_t st) {
+int launch_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* x_edge, const void* m, const void* const* maa, int reverse,
+                    void* const* out, cudaStream_t st) {
     TmixArgs a;
     a.x = x;
+    a.x_edge = x_edge;
     a.m = m;
     for (int i = 0; i < 5; i++) a.maa[i] = maa[i];
     for (int i = 0; i < 4; i++) a.out[i] = out[i];

@@ -198,11 +198,12 @@ def combine(a: torch.Tensor, b: Optional[torch.Tensor], scale: float = 0.5, roun
     return out
 
 
-def tmix_mix(x: torch.Tensor, maa_x: torch.Tensor, maa_rkvw, w1: torch.Tensor, w2: torch.Tensor, reverse: bool = False):
+def tmix_mix(x: torch.Tensor, maa_x: torch.Tensor, maa_rkvw, w1: torch.Tensor, w2: torch.Tensor, reverse: bool = False,
+             x_edge: Optional[torch.Tensor] = None):
     """Token shift + the five `maa` mixes of RWKV_Tmix_x060c.forward (model.py:270-289) with the two elementwise
     stages fused (one kernel each, bit-exact with the eager ops); the LoRA GEMMs in between stay library calls.
-    x [B,T,C] contiguous; maa_* [1,1,C]; w1 [C,128], w2 [4,32,C].  Returns x_r, x_k, x_v, x_w.  Inference only (no
-    autograd graph is recorded)."""
+    x [B,T,C] contiguous; maa_* [1,1,C]; w1 [C,128], w2 [4,32,C]; x_edge [B,C] = the frame beyond the edge (streaming)
+    or None (zeros).  Returns x_r, x_k, x_v, x_w.  Inference only (no autograd graph is recorded)."""
     assert x.is_cuda and x.is_contiguous() and x.dim() == 3
     B, T, C = x.shape
     L, dt, st = _lib.lib(), _dtype_code(x), _stream(x)
@@ -210,12 +211,14 @@ def tmix_mix(x: torch.Tensor, maa_x: torch.Tensor, maa_rkvw, w1: torch.Tensor, w
     mx = flat(maa_x)
     mr, mk, mv, mw = (flat(t) for t in maa_rkvw)
     xxx = torch.empty_like(x)
+    if x_edge is not None:
+        x_edge = x_edge.detach().to(x.dtype).reshape(B, C).contiguous()
     with torch.cuda.device(x.device):
-        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), None, _p(mx), None, None, None, None, int(bool(reverse)),
+        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), _p(x_edge), None, _p(mx), None, None, None, None, int(bool(reverse)),
                                         _p(xxx), None, None, None, None, st))
         m = torch.tanh(xxx.view(B * T, C) @ w1.detach()).view(B * T, 4, -1).transpose(0, 1)
         m = torch.bmm(m, w2.detach()).contiguous()                      # [4, B*T, C]
         outs = [torch.empty_like(x) for _ in range(4)]
-        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), _p(m), None, _p(mr), _p(mk), _p(mv), _p(mw), int(bool(reverse)),
+        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), _p(x_edge), _p(m), None, _p(mr), _p(mk), _p(mv), _p(mw), int(bool(reverse)),
                                         None, *[_p(o) for o in outs], st))
     return tuple(outs)

@@ -64,18 +64,23 @@ class RWKV_Tmix_x060c(nn.Module):
         self.output = nn.Linear(dim_att, n_embd, bias=False)
         self.ln_x = nn.LayerNorm(dim_att)
 
-    def prologue(self, x: torch.Tensor, reverse: bool = False):
-        """x [B,T,C] -> contiguous r, k, v, w (model.py:270-289).  `reverse`: the token shift looks at t+1."""
+    def prologue(self, x: torch.Tensor, reverse: bool = False, x_edge: Optional[torch.Tensor] = None):
+        """x [B,T,C] -> contiguous r, k, v, w (model.py:270-289).  `reverse`: the token shift looks at t+1.
+        `x_edge` [B,C]: the frame beyond the edge the shift looks across (streaming: last frame of the previous piece);
+        None = zeros, as at the start of an utterance."""
         B, T, C = x.size()
         if x.is_cuda and not torch.is_grad_enabled() and x.dtype in (torch.bfloat16, torch.float32) and C % 8 == 0:
             # inference: the elementwise stages run fused (ops.tmix_mix, bit-exact with the eager ops below)
             xr, xk, xv, ww = ops.tmix_mix(x.contiguous(), self.time_maa_x,
                                           (self.time_maa_r, self.time_maa_k, self.time_maa_v, self.time_maa_w),
-                                          self.time_maa_rkvw_w1, self.time_maa_rkvw_w2, reverse)
+                                          self.time_maa_rkvw_w1, self.time_maa_rkvw_w2, reverse, x_edge)
             w = self.time_decay + torch.tanh(ww @ self.time_decay_w1) @ self.time_decay_w2
             return (self.receptance(xr).contiguous(), self.key(xk).contiguous(), self.value(xv).contiguous(),
                     w.contiguous())
-        if reverse:
+        if x_edge is not None:
+            e = x_edge.to(x.dtype).view(B, 1, C)
+            xx = (torch.cat([x[:, 1:], e], 1) if reverse else torch.cat([e, x[:, :-1]], 1)) - x
+        elif reverse:
             xx = F.pad(x[:, 1:], (0, 0, 0, 1)) - x
         else:
             xx = F.pad(x[:, :-1], (0, 0, 1, 0)) - x                      # nn.ZeroPad2d((0,0,1,-1))
@@ -102,6 +107,14 @@ class RWKV_Tmix_x060c(nn.Module):
         else:
             y = autograd.RUN_CUDA_RWKV6(r, k, v, w, self.time_faaaa)
         return self.epilogue(y)
+
+    def forward_stream(self, x: torch.Tensor, state: Optional[torch.Tensor], x_last: Optional[torch.Tensor]):
+        """One piece of a left-to-right stream: `state` [B,H,N,N] fp32 is the WKV state after the previous
+        piece, `x_last` [B,C] its last input frame (None, None at the start of an utterance).  Returns (out, new_state,
+        new_x_last); the pieces' outputs concatenated equal the output of one call over the whole utterance."""
+        r, k, v, w = self.prologue(x, False, x_last)
+        y, s_new = autograd.wkv6(r, k, v, w, self.time_faaaa, state, False)
+        return self.epilogue(y), s_new, x[:, -1]
 
 
 _EMPTY_MASK = torch.ones((0, 0, 0), dtype=torch.bool)
@@ -130,10 +143,25 @@ class RWKV_TmixWrapper(nn.Module):
                 ) -> Tuple[torch.Tensor, torch.Tensor]:
         qd = query.dtype
         x = query.to(dtype=torch.bfloat16) if self.do_bfloat16 else query
+        if cache.numel() > 0:
+            # streaming (the reference passes the cache through untouched, rwkv_wrapper.py:81): the cache
+            # carries the WKV state and the last input frame, see init_cache()
+            B, C, nn_ = x.shape[0], self.n_embd, self.n_head * self.head_size * self.head_size
+            assert cache.shape == (B, nn_ + C) and cache.dtype == torch.float32, "cache: see RWKV_TmixWrapper.init_cache"
+            state = cache[:, :nn_].reshape(B, self.n_head, self.head_size, self.head_size).contiguous()
+            out, s_new, x_last = self.tmix_block.forward_stream(x, state, cache[:, nn_:].to(x.dtype).contiguous())
+            new_cache = torch.cat([s_new.reshape(B, nn_).float(), x_last.float()], 1)
+            return (out.to(dtype=qd) if self.do_bfloat16 else out), new_cache
         out = self.tmix_block(x)
         if self.do_bfloat16:
             out = out.to(dtype=qd)
         return out, cache
+
+    def init_cache(self, batch: int, device=None) -> torch.Tensor:
+        """Cache of a stream that has seen nothing yet: [B, H*N*N + C] fp32 = WKV state [B,H,N,N] (zeros) followed by the
+        last input frame (zeros: the token shift of frame 0 sees zero, model.py:272).  Pass it as `cache`; every call
+        returns the cache for the next piece."""
+        return torch.zeros(batch, self.n_head * self.head_size * self.head_size + self.n_embd, dtype=torch.float32, device=device)
 
 
 def _bi_block(fwd: RWKV_Tmix_x060c, bwd: RWKV_Tmix_x060c, x: torch.Tensor, run_l2r: bool, run_r2l: bool):

@@ -30,12 +30,12 @@ st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 def fused1():
     for l in range(NL):
-        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), None, p(maa[0]), None, None, None, None, 0, p(out1[l]), None, None, None, None, st))
+        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), None, None, p(maa[0]), None, None, None, None, 0, p(out1[l]), None, None, None, None, st))
 
 
 def fused2():
     for l in range(NL):
-        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), p(ms[l]), None, p(maa[1]), p(maa[2]), p(maa[3]), p(maa[4]), 0, None,
+        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), None, p(ms[l]), None, p(maa[1]), p(maa[2]), p(maa[3]), p(maa[4]), 0, None,
                                         *[p(o) for o in out2[l]], st))
 
 

@@ -46,21 +46,25 @@ def make_inputs(B, T, H, N, seed=777, dtype=torch.float64, layer=0, n_layers=12,
     return {kk_: vv_.to(dtype) for kk_, vv_ in out.items()}
 
 
-def tmix_shift(x, reverse=False):
+def tmix_shift(x, reverse=False, x_edge=None):
     """xx = shift(x) - x of RWKV_Tmix_x060c.forward (wenet/rwkv_v6/src/model.py:272-273: nn.ZeroPad2d((0,0,1,-1)));
-    `reverse`: the flip-free right-to-left block looks at t+1 instead."""
+    `reverse`: the flip-free right-to-left block looks at t+1 instead; `x_edge` [B,C]: the frame
+    beyond the edge instead of the zero padding (streaming)."""
     import torch.nn.functional as F
+    if x_edge is not None:
+        e = x_edge.view(x.shape[0], 1, x.shape[2])
+        return (torch.cat([x[:, 1:], e], 1) if reverse else torch.cat([e, x[:, :-1]], 1)) - x
     if reverse:
         return F.pad(x[:, 1:], (0, 0, 0, 1)) - x
     return F.pad(x[:, :-1], (0, 0, 1, 0)) - x
 
 
-def tmix_mix_stage1(x, maa_x, reverse=False):
+def tmix_mix_stage1(x, maa_x, reverse=False, x_edge=None):
     """model.py:275: xxx = x + xx * time_maa_x (eager ops in x's dtype)."""
-    return x + tmix_shift(x, reverse) * maa_x
+    return x + tmix_shift(x, reverse, x_edge) * maa_x
 
 
-def tmix_mix_stage2(x, m, maa_r, maa_k, maa_v, maa_w, reverse=False):
+def tmix_mix_stage2(x, m, maa_r, maa_k, maa_v, maa_w, reverse=False, x_edge=None):
     """model.py:280-287: x + xx * (time_maa_c + m_c) for c in r, k, v, w; m is [4,B,T,C]."""
-    xx = tmix_shift(x, reverse)
+    xx = tmix_shift(x, reverse, x_edge)
     return tuple(x + xx * (maa + mc) for maa, mc in zip((maa_r, maa_k, maa_v, maa_w), m.unbind(0)))

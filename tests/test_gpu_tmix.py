@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 SHAPES = [(2, 250, 256), (1, 1, 64), (3, 2, 64), (2, 77, 512), (1, 1031, 1024)]
 
 
-def _call(x, m, maa, reverse):
+def _call(x, m, maa, reverse, x_edge=None):
     from paper_accurate_fast_cheap_b200 import _lib, ops
     B, T, C = x.shape
     L = _lib.lib()
@@ -23,12 +23,12 @@ def _call(x, m, maa, reverse):
     n0 = _lib.launch_count()
     if m is None:
         out = torch.empty_like(x)
-        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, p(x), None, p(maa[0]), None, None, None, None, int(reverse), p(out),
+        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, p(x), p(x_edge), None, p(maa[0]), None, None, None, None, int(reverse), p(out),
                                         None, None, None, None, st))
         res = (out,)
     else:
         outs = [torch.empty_like(x) for _ in range(4)]
-        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, p(x), p(m), None, p(maa[1]), p(maa[2]), p(maa[3]), p(maa[4]), int(reverse),
+        _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, p(x), p(x_edge), p(m), None, p(maa[1]), p(maa[2]), p(maa[3]), p(maa[4]), int(reverse),
                                         None, *[p(o) for o in outs], st))
         res = tuple(outs)
     assert _lib.launch_count() - n0 == 1
@@ -36,20 +36,23 @@ def _call(x, m, maa, reverse):
     return res
 
 
+@pytest.mark.parametrize("edge", [False, True], ids=["zero_edge", "edge_frame"])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("reverse", [False, True])
 @pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "x".join(map(str, s)))
-def test_tmix_mix_bit_exact(shape, reverse, dtype):
+def test_tmix_mix_bit_exact(shape, reverse, dtype, edge):
     B, T, C = shape
     g = torch.Generator().manual_seed(B * 1000 + T + C)
     x = torch.randn(B, T, C, generator=g).to(dtype)
+    xe = torch.randn(B, C, generator=g).to(dtype) if edge else None
+    xed = xe.cuda() if edge else None
     m = (0.3 * torch.randn(4, B, T, C, generator=g)).to(dtype)
     maa = [torch.rand(1, 1, C, generator=g).to(dtype) for _ in range(5)]
     xd, md, maad = x.cuda(), m.cuda(), [t.cuda().reshape(-1).contiguous() for t in maa]
-    (xxx,) = _call(xd, None, maad, reverse)
-    assert torch.equal(xxx.cpu(), ref.tmix_mix_stage1(x, maa[0], reverse))
-    outs = _call(xd, md, maad, reverse)
-    want = ref.tmix_mix_stage2(x, m, maa[1], maa[2], maa[3], maa[4], reverse)
+    (xxx,) = _call(xd, None, maad, reverse, xed)
+    assert torch.equal(xxx.cpu(), ref.tmix_mix_stage1(x, maa[0], reverse, xe))
+    outs = _call(xd, md, maad, reverse, xed)
+    want = ref.tmix_mix_stage2(x, m, maa[1], maa[2], maa[3], maa[4], reverse, xe)
     for name, a, b in zip("rkvw", outs, want):
         assert torch.equal(a.cpu(), b), name
 
