@@ -176,7 +176,8 @@ static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets
         e = launch_fwd_chunk_segmented(p, g_scratch, g_scratch_bytes, (cudaStream_t)stream);
         if (e < 0) e = launch_fwd_chunk(p, (cudaStream_t)stream);
     } else {
-        e = launch_fwd_scan(dtype, p, (cudaStream_t)stream);
+        e = launch_fwd_scan_segmented(dtype, p, g_scratch, g_scratch_bytes, (cudaStream_t)stream);
+        if (e < 0) e = launch_fwd_scan(dtype, p, (cudaStream_t)stream);
     }
     return cuda_fail(e, "wkv6 forward launch");
 }

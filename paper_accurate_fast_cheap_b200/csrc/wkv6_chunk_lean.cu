@@ -529,23 +529,33 @@ static int pick_segments(const Params& p, size_t scratch_bytes, int* seg_chunks)
 
 int launch_fwd_chunk_lean(const Params& p, cudaStream_t st);
 
-// Segmented forward: pass 1, scan, pass 2 on the caller's scratch buffer.  Returns -1 when the launch does not qualify.
-int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+// Fills the segmentation fields of q (number of segments, chunks per segment, scratch layout); false: run unsegmented.
+bool plan_segments(Params& q, void* scratch, size_t scratch_bytes) {
     int sc = 0;
-    const int nseg = scratch ? pick_segments(p, scratch_bytes, &sc) : 0;
-    if (nseg == 0) return -1;
-    const int nseq = p.ndir * p.B * p.H;
-    Params q = p;
+    const int nseg = scratch ? pick_segments(q, scratch_bytes, &sc) : 0;
+    if (nseg == 0) return false;
+    const int nseq = q.ndir * q.B * q.H;
     q.nseg = nseg;
     q.seg_chunks = sc;
     q.seg_state = static_cast<float*>(scratch);
     q.seg_decay = q.seg_state + (size_t)nseq * nseg * N * N;
+    return true;
+}
+
+int launch_seg_scan(const Params& q, cudaStream_t st) {
+    wkv6_seg_scan_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), 0, st>>>(q);
+    count_launch(1);
+    return (int)cudaGetLastError();
+}
+
+// Segmented forward: pass 1, scan, pass 2 on the caller's scratch buffer.  Returns -1 when the launch does not qualify.
+int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    Params q = p;
+    if (!plan_segments(q, scratch, scratch_bytes)) return -1;
     q.seg_mode = 1;
     int e = launch_fwd_chunk_lean(q, st);
     if (e) return e;
-    wkv6_seg_scan_kernel<<<dim3(nseq), dim3(256), 0, st>>>(q);
-    count_launch(1);
-    if ((e = (int)cudaGetLastError())) return e;
+    if ((e = launch_seg_scan(q, st))) return e;
     q.seg_mode = 2;
     return launch_fwd_chunk_lean(q, st);
 }

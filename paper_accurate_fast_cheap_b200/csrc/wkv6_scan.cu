@@ -132,13 +132,38 @@ __global__ void __launch_bounds__(NT, 2) wkv6_fwd_scan_kernel(const __grid_const
     const int tid = threadIdx.x;
     const Tile tl(tid);
     const int BH = p.B * p.H;
-    const int ds = blockIdx.x / BH;
-    const int bh = blockIdx.x - ds * BH;
+    const int nseg = p.nseg > 1 ? p.nseg : 1;
+    const int seq = blockIdx.x / nseg, seg = blockIdx.x - seq * nseg;
+    const int ds = seq / BH;
+    const int bh = seq - ds * BH;
     const int b = bh / p.H, h = bh - b * p.H;
     const DirArgs& D = p.d[ds];
     const bool rev = D.reverse != 0;
     const int T = p.T, C = p.C;
-    const int ntiles = (T + TT - 1) / TT;
+    const int ntot = (T + TT - 1) / TT;
+
+    // The CTA walks the tiles [tbeg, tbeg + ntiles) of its sequence in processing order.  Time-segmented launch (long
+    // sequences, few of them; see launch_fwd_scan_segmented): pass 1 starts every segment from S = 0, writes no y and
+    // leaves the segment's final state and the product of its per-step decays in the scratch; pass 2 starts from the
+    // segment-start state the scan kernel put there.
+    int tbeg = 0, ntiles = ntot;
+    const float* s0p = D.s0 ? D.s0 + (size_t)bh * N * N : nullptr;
+    float* sTp = D.sT ? D.sT + (size_t)bh * N * N : nullptr;
+    float* decay_out = nullptr;
+    bool write_y = true;
+    if (p.nseg > 1) {
+        const int per = p.seg_chunks * (64 / TT);
+        tbeg = seg * per;
+        ntiles = min(per, ntot - tbeg);
+        float* slot = p.seg_state + ((size_t)seq * nseg + seg) * N * N;
+        if (p.seg_mode == 1) {
+            s0p = nullptr; sTp = slot; write_y = false;
+            decay_out = p.seg_decay + ((size_t)seq * nseg + seg) * N;
+        } else {
+            s0p = slot;
+            if (seg != nseg - 1) sTp = nullptr;
+        }
+    }
 
     if (tid == 0) {
 #pragma unroll
@@ -148,8 +173,8 @@ __global__ void __launch_bounds__(NT, 2) wkv6_fwd_scan_kernel(const __grid_const
     }
     __syncthreads();
 
-    auto issue = [&](int n) {
-        const int q = rev ? ntiles - 1 - n : n;
+    auto issue = [&](int n) {   // n: local tile index
+        const int q = rev ? ntot - 1 - (tbeg + n) : tbeg + n;
         const int slot = n % NS;
         mbar_arrive_expect_tx(&sm.full[slot], 4u * TT * N * sizeof(IO));
         tma_load_3d(sm.raw[slot][0], &D.mr, &sm.full[slot], h * N, q * TT, b);
@@ -166,7 +191,10 @@ __global__ void __launch_bounds__(NT, 2) wkv6_fwd_scan_kernel(const __grid_const
     tr::load8(reinterpret_cast<const IO*>(D.u) + h * N + pc0, u8);
 
     float2 S[4][4];
-    load_state(S, D.s0 ? D.s0 + (size_t)bh * N * N : nullptr, tl);
+    load_state(S, s0p, tl);
+    float2 dprod[4];   // product of the per-step decays of this thread's 8 key channels (segmented pass 1)
+#pragma unroll
+    for (int qq = 0; qq < 4; qq++) dprod[qq] = make_float2(1.f, 1.f);
 
     auto preprocess = [&](int n) {
         const int slot = n % NS, buf = n & 1;
@@ -219,13 +247,17 @@ __global__ void __launch_bounds__(NT, 2) wkv6_fwd_scan_kernel(const __grid_const
             }
             ya[a] = acc.x + acc.y;
         }
+        if (decay_out) {
+#pragma unroll
+            for (int qq = 0; qq < 4; qq++) dprod[qq] = __fmul2_rn(dprod[qq], d2[qq]);
+        }
         *reinterpret_cast<float4*>(&sm.part[(s * 8 + tl.jg) * PSTR + tl.i0]) = make_float4(ya[0], ya[1], ya[2], ya[3]);
     };
 
     if (ntiles > 0) preprocess(0);
     for (int n = 0; n < ntiles; n++) {
         const int buf = n & 1;
-        const int q = rev ? ntiles - 1 - n : n;
+        const int q = rev ? ntot - 1 - (tbeg + n) : tbeg + n;
         const int nvalid = min(TT, T - q * TT);
         __syncthreads();   // f[buf] complete; previous epilogue done with `part`
         if (tid == 0 && n + NS < ntiles) issue(n + NS);
@@ -241,7 +273,7 @@ __global__ void __launch_bounds__(NT, 2) wkv6_fwd_scan_kernel(const __grid_const
             for (int m = 0; m < nvalid; m++) step(buf, rev ? nvalid - 1 - m : m);
         }
         __syncthreads();
-        if (prow < nvalid) {
+        if (write_y && prow < nvalid) {
             float o8[8], a8[8];
             ld8f(&sm.f[buf][2][prow * N + pc0], o8);
             const float bn = sm.bonus[buf][prow];
@@ -257,7 +289,11 @@ __global__ void __launch_bounds__(NT, 2) wkv6_fwd_scan_kernel(const __grid_const
         }
         if (n + 1 < ntiles) preprocess(n + 1);
     }
-    if (D.sT) store_state(S, D.sT + (size_t)bh * N * N, tl);
+    if (sTp) store_state(S, sTp, tl);
+    if (decay_out && tl.i0 == 0) {
+        *reinterpret_cast<float4*>(decay_out + tl.jA) = make_float4(dprod[0].x, dprod[0].y, dprod[1].x, dprod[1].y);
+        *reinterpret_cast<float4*>(decay_out + tl.jB) = make_float4(dprod[2].x, dprod[2].y, dprod[3].x, dprod[3].y);
+    }
 }
 
 // =======================================================================================
@@ -715,13 +751,26 @@ static int launch_fwd_t(const Params& p, cudaStream_t st) {
     const size_t smem = sizeof(FwdSmem<IO>);
     cudaError_t e = set_smem(wkv6_fwd_scan_kernel<IO>, smem);
     if (e != cudaSuccess) return (int)e;
-    wkv6_fwd_scan_kernel<IO><<<dim3(p.ndir * p.B * p.H), dim3(NT), smem, st>>>(p);
+    wkv6_fwd_scan_kernel<IO><<<dim3(p.ndir * p.B * p.H * (p.nseg > 1 ? p.nseg : 1)), dim3(NT), smem, st>>>(p);
     count_launch(1);
     return (int)cudaGetLastError();
 }
 
 int launch_fwd_scan(int dtype, const Params& p, cudaStream_t st) {
     return dtype == 0 ? launch_fwd_t<__nv_bfloat16>(p, st) : launch_fwd_t<float>(p, st);
+}
+
+// Time-segmented exact scan (same scheme as launch_fwd_chunk_segmented, same scratch layout and segment rule): pass 1,
+// segment scan, pass 2.  Returns -1 when the launch does not qualify.
+int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    Params q = p;
+    if (!plan_segments(q, scratch, scratch_bytes)) return -1;
+    q.seg_mode = 1;
+    int e = launch_fwd_scan(dtype, q, st);
+    if (e) return e;
+    if ((e = launch_seg_scan(q, st))) return e;
+    q.seg_mode = 2;
+    return launch_fwd_scan(dtype, q, st);
 }
 
 template <typename IO>

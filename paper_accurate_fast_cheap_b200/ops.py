@@ -53,7 +53,7 @@ SCRATCH_BYTES = 6 << 20      # covers every segmented launch (<= 296 segment slo
 def _lend_scratch(t: torch.Tensor) -> None:
     """Long sequences with few (batch, head) pairs run time-segmented (include/wkv6_b200.h: wkv6_b200_set_scratch); the
     library never allocates, so the host side lends it a small per-device buffer once (torch caching allocator)."""
-    if t.dtype != torch.bfloat16 or t.size(1) < 2048:
+    if t.size(1) < 2048:
         return
     key = t.device.index
     if key not in _SCRATCH:

@@ -161,3 +161,45 @@ def test_time_segmented_ragged_and_speed():
     assert oracle.rel_err(y0, y_ref) <= TOL[torch.bfloat16]
     print(f"T={T} 4 sequences: one CTA per sequence {t_plain:.3f} ms, time-segmented {t_seg:.3f} ms")
     assert t_seg < 0.5 * t_plain
+
+
+@pytest.mark.parametrize("with_state", [False, True])
+def test_time_segmented_fp32_scan(with_state):
+    """The exact fp32 scan takes the same time-segmented route (configs[4]: one 1-hour utterance per GPU = 32 sequences
+    on 148 SMs): three launches, y and S_T within the fp32 tolerance of the fp64 oracle and of the unsegmented run,
+    ragged T, both directions, with and without an initial state; and it is faster."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import ops
+    B, T, H = 1, 20011, 4
+    a = _inputs(B, T, H, torch.float32, with_state=with_state, seed=61)
+    b = _inputs(B, T, H, torch.float32, with_state=with_state, seed=62, layer=5)
+    ga, gb = _cuda(a), _cuda(b)
+    f, r_ = tuple(ga[n] for n in "rkvwu"), tuple(gb[n] for n in "rkvwu")
+    kw = dict(s0_f=ga.get("s0"), s0_b=gb.get("s0"), want_state=True)
+
+    def timed():
+        pk.bi_forward_raw(f, r_, **kw)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = pk.launch_count()
+        e0.record()
+        out = pk.bi_forward_raw(f, r_, **kw)
+        e1.record()
+        torch.cuda.synchronize()
+        return out, e0.elapsed_time(e1), pk.launch_count() - n0
+
+    ops.set_segmentation(False)
+    try:
+        plain, t_plain, n_plain = timed()
+    finally:
+        ops.set_segmentation(True)
+    seg, t_seg, n_seg = timed()
+    assert n_plain == 1 and n_seg == 3
+    ya, sa = oracle.fwd(a["r"], a["k"], a["v"], a["w"], a["u"], a.get("s0"), want_state=True, prec="f64")
+    yb, sb = oracle.fwd(b["r"], b["k"], b["v"], b["w"], b["u"], b.get("s0"), rev=True, want_state=True, prec="f64")
+    tol = TOL[torch.float32]
+    for got in (plain, seg):
+        assert oracle.rel_err(got[0], ya) <= tol and oracle.rel_err(got[1], yb) <= tol
+        assert oracle.rel_err(got[2], sa) <= tol and oracle.rel_err(got[3], sb) <= tol
+    print(f"fp32 scan, 8 sequences of T={T}: one CTA per sequence {t_plain:.3f} ms, time-segmented {t_seg:.3f} ms")
+    assert t_seg < 0.6 * t_plain
