@@ -490,24 +490,31 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
 }
 
 // Segment scan: S_start[0] = S_0 (or 0), S_start[s+1][i][j] = S_start[s][i][j] * D_s[j] + dS_s[i][j]; the slots that pass 1
-// filled with dS_s are overwritten with S_start[s].  One CTA per (direction, batch, head), one state element per thread
-// and iteration: coalesced, a few microseconds.
+// filled with dS_s are overwritten with S_start[s].  One thread per state element, grid = sequences x 16: every thread
+// first loads its element of all segments (independent loads, all in flight), then runs the recurrence from registers.
+constexpr int kMaxSeg = 40;   // pick_segments: nseg <= 296 / 8 = 37
 __global__ void __launch_bounds__(256) wkv6_seg_scan_kernel(const __grid_constant__ Params p) {
     const int BH = p.B * p.H;
-    const int seq = blockIdx.x, ds = seq / BH, bh = seq - ds * BH;
+    const int seq = blockIdx.x >> 4, ds = seq / BH, bh = seq - ds * BH;
+    const int e = ((blockIdx.x & 15) << 8) + threadIdx.x;   // element i * N + j of the state
+    const int j = e & (N - 1);
     const DirArgs& D = p.d[ds];
-    const float* s0 = D.s0 ? D.s0 + (size_t)bh * N * N : nullptr;
-    float* st = p.seg_state + (size_t)seq * p.nseg * N * N;
-    const float* dec = p.seg_decay + (size_t)seq * p.nseg * N;
-    for (int e = threadIdx.x; e < N * N; e += 256) {
-        const int j = e & (N - 1);
-        float cur = s0 ? s0[e] : 0.f;
-        for (int s = 0; s < p.nseg; s++) {
-            const float ds_ = st[(size_t)s * N * N + e];
-            st[(size_t)s * N * N + e] = cur;
-            cur = fmaf(cur, dec[s * N + j], ds_);
+    float* st = p.seg_state + (size_t)seq * p.nseg * N * N + e;
+    const float* dec = p.seg_decay + (size_t)seq * p.nseg * N + j;
+    float dS[kMaxSeg], dk[kMaxSeg];
+#pragma unroll
+    for (int s = 0; s < kMaxSeg; s++)
+        if (s < p.nseg) {
+            dS[s] = st[(size_t)s * N * N];
+            dk[s] = dec[s * N];
         }
-    }
+    float cur = D.s0 ? D.s0[(size_t)bh * N * N + e] : 0.f;
+#pragma unroll
+    for (int s = 0; s < kMaxSeg; s++)
+        if (s < p.nseg) {
+            st[(size_t)s * N * N] = cur;
+            cur = fmaf(cur, dk[s], dS[s]);
+        }
 }
 
 // Number of time segments for a launch (0 = unsegmented): only when one CTA per sequence leaves most SMs empty and the
@@ -543,7 +550,8 @@ bool plan_segments(Params& q, void* scratch, size_t scratch_bytes) {
 }
 
 int launch_seg_scan(const Params& q, cudaStream_t st) {
-    wkv6_seg_scan_kernel<<<dim3(q.ndir * q.B * q.H), dim3(256), 0, st>>>(q);
+    if (q.nseg > kMaxSeg) return (int)cudaErrorInvalidValue;
+    wkv6_seg_scan_kernel<<<dim3(q.ndir * q.B * q.H * 16), dim3(256), 0, st>>>(q);
     count_launch(1);
     return (int)cudaGetLastError();
 }
