@@ -66,8 +66,8 @@ const char* wkv6_b200_last_error(void);
 /* Number of kernels this library has launched since load (the bench's gpu_launches). */
 long long wkv6_b200_launch_count(void);
 /* Optional: lend a device scratch buffer (caller-owned, >= 16-byte aligned) to the library.  With it, forward calls
- * (either dtype) whose sequences are long (>= 2048 steps) and few (directions * B * H <= 74) run time-segmented (two passes over
- * 4..37 segments per sequence) instead of one CTA per sequence; 5 MB covers every case.  NULL / 0 takes it back. */
+ * (either dtype) whose sequences are long (>= 2048 steps) and few (directions * B * H <= 148 for bf16, <= 74 for f32) run
+ * time-segmented (two passes over 2..37 segments per sequence) instead of one CTA per sequence; 5 MB covers every case.  NULL / 0 takes it back. */
 int  wkv6_b200_set_scratch(void* device_ptr, size_t bytes);
 /* Debug aid: clock64() trace of one CTA of the chunk kernels (see csrc/wkv6_capi.cu); not part of the data path. */
 int  wkv6_b200_debug_trace(int enable, unsigned long long* out);

@@ -249,13 +249,16 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             sts64(kt_u32 + vb_own + offs[r], ko2[r][0], ko2[r][1]);
         }
     };
+    // state-only mode (pass 1 of a time-segmented launch): no y, so no P^T (G1), no G2 / G3 and no R-side tiles; what is
+    // left per chunk is the decays, Ktil relative to the chunk end, dS (G4) and the state update -- under half the work
+    const bool so = decay_out != nullptr && skip_y && !ckpt_on;
     auto phase2 = [&](const int c) {
         const float* bt = &sm.blocktot[c & 1][0][0];
         switch (I) {   // warp-uniform
-            case 0: lean_phase2<0>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 1: lean_phase2<1>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 2: lean_phase2<2>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            default: lean_phase2<3>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 0: lean_phase2<0>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, so); break;
+            case 1: lean_phase2<1>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, so); break;
+            case 2: lean_phase2<2>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, so); break;
+            default: lean_phase2<3>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, so); break;
         }
     };
     // ---- MMAs that do not need P^T: G1 (four groups, four issuing lanes), G3 + G4 (one lane); checkpoint store
@@ -263,6 +266,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         if (warp < 5 && elect_one()) {
             tc_fence_after();
             if (warp < 4) {
+                if (so) goto front_done;
                 const int rowlo = REV ? 48 - 16 * warp : 16 * warp;
                 const int vbi = warp == 0 ? ktbase(REV, 0) : warp == 1 ? ktbase(REV, 1) : warp == 2 ? ktbase(REV, 2) : ktbase(REV, 3);
 #pragma unroll
@@ -272,13 +276,16 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             } else {
                 const uint64_t dm_v = (c & 1) ? dm_v1 : dm_v0;
                 mbar_wait(&sm.bar_v[c & 1], (c >> 1) & 1);
+                if (!so) {
 #pragma unroll
-                for (int ks = 0; ks < 4; ks++) umma(tY, dk_rst + DOFF(ks * 32), dm_sp + DOFF(ks * 2048), ID_G3, ks > 0);
+                    for (int ks = 0; ks < 4; ks++) umma(tY, dk_rst + DOFF(ks * 32), dm_sp + DOFF(ks * 2048), ID_G3, ks > 0);
+                }
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++)
                     umma(tD, dm_kt + DOFF(ktbase(REV, 4) + ks * 2048), dm_v + DOFF(ks * 2048), ID_G2, ks > 0);
                 umma_commit(&sm.bar_s);
             }
+        front_done:;
         }
         if (TMA_THR && ckpt_on) {   // S at the start of chunk c (bf16, [j][i]) -> checkpoint c of this sequence
             tma_store_2d(&D.mc, sm.sp, 0, (bh * ntot + cbeg + c) * N);
@@ -309,6 +316,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         if (p.dbg && blockIdx.x == 0 && tid == 0 && c < 32) p.dbg[32 + c] = clock64();   // loop-top stamp of every chunk
 
         // ---------------- P^T readout: causal mask + bonus diagonal -> bf16 tile (MN-major A of G2)
+        if (!so) {
         mbar_wait(&sm.bar_p, par);
         WKV6_TS(0, 1);
         tc_fence_after();
@@ -362,6 +370,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             umma_commit(&sm.bar_y);
         }
         __syncwarp();
+        }   // !so
 
         // ---------------- state update (under G2):  S^T[j][i] = S^T[j][i] 2^(A_L[j]) + dS^T[j][i]
         mbar_wait(&sm.bar_s, par);
@@ -382,7 +391,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
                 st[4 * rep + 2] = fmaf(st[4 * rep + 2], f1, dv[4 * rep + 2]);
                 st[4 * rep + 3] = fmaf(st[4 * rep + 3], f1, dv[4 * rep + 3]);
             }
-            store_frag(sp_u32, st);
+            if (!so) store_frag(sp_u32, st);
         }
         WKV6_TS(0, 5);
 
@@ -398,7 +407,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         }
 
         // ---------------- Y readout -> bf16 staging tile -> TMA store
-        mbar_wait(&sm.bar_y, par);
+        if (!so) mbar_wait(&sm.bar_y, par);
         WKV6_TS(0, 9);
         tc_fence_after();
         if (!skip_y) {
@@ -517,15 +526,16 @@ __global__ void __launch_bounds__(256) wkv6_seg_scan_kernel(const __grid_constan
         }
 }
 
-// Number of time segments for a launch (0 = unsegmented): only when one CTA per sequence leaves most SMs empty and the
-// sequences are long; two passes cost ~2x the work, so at least 4 segments, each at least 8 chunks long.
-static int pick_segments(const Params& p, size_t scratch_bytes, int* seg_chunks) {
+// Number of time segments for a launch (0 = unsegmented): only when one CTA per sequence leaves SM slots empty and the
+// sequences are long.  The two passes cost 2x the work of one for the exact scan and ~1.75x for the chunk kernel (its
+// pass 1 is state-only), so at least min_seg segments (4 / 2), each at least 8 chunks long.
+static int pick_segments(const Params& p, size_t scratch_bytes, int min_seg, int* seg_chunks) {
     const int nseq = p.ndir * p.B * p.H;
     const int ntot = (p.T + CL - 1) / CL;
-    if (nseq <= 0 || nseq > 74 || ntot < 32) return 0;
+    if (nseq <= 0 || nseq * min_seg > 296 || ntot < 32) return 0;
     int nseg = 296 / nseq;                       // 148 SMs x 2 resident CTAs
     if (nseg > ntot / 8) nseg = ntot / 8;
-    if (nseg < 4) return 0;
+    if (nseg < min_seg) return 0;
     int sc = (ntot + nseg - 1) / nseg;
     nseg = (ntot + sc - 1) / sc;                 // no empty segments
     const size_t need = (size_t)nseq * nseg * (N * N + N) * sizeof(float);
@@ -537,9 +547,9 @@ static int pick_segments(const Params& p, size_t scratch_bytes, int* seg_chunks)
 int launch_fwd_chunk_lean(const Params& p, cudaStream_t st);
 
 // Fills the segmentation fields of q (number of segments, chunks per segment, scratch layout); false: run unsegmented.
-bool plan_segments(Params& q, void* scratch, size_t scratch_bytes) {
+bool plan_segments(Params& q, void* scratch, size_t scratch_bytes, int min_seg) {
     int sc = 0;
-    const int nseg = scratch ? pick_segments(q, scratch_bytes, &sc) : 0;
+    const int nseg = scratch ? pick_segments(q, scratch_bytes, min_seg, &sc) : 0;
     if (nseg == 0) return false;
     const int nseq = q.ndir * q.B * q.H;
     q.nseg = nseg;
@@ -559,7 +569,7 @@ int launch_seg_scan(const Params& q, cudaStream_t st) {
 // Segmented forward: pass 1, scan, pass 2 on the caller's scratch buffer.  Returns -1 when the launch does not qualify.
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
     Params q = p;
-    if (!plan_segments(q, scratch, scratch_bytes)) return -1;
+    if (!plan_segments(q, scratch, scratch_bytes, 2)) return -1;
     q.seg_mode = 1;
     int e = launch_fwd_chunk_lean(q, st);
     if (e) return e;

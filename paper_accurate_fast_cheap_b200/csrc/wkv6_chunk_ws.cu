@@ -294,10 +294,10 @@ __device__ __forceinline__ void ws_compute(const Params& p, WsSmem& sm, const Di
     auto phase2 = [&](const int c) {
         const float* bt = &sm.blocktot[c & 1][0][0];
         switch (I) {   // warp-uniform
-            case 0: lean_phase2<0>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 1: lean_phase2<1>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            case 2: lean_phase2<2>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
-            default: lean_phase2<3>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2); break;
+            case 0: lean_phase2<0>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, false); break;
+            case 1: lean_phase2<1>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, false); break;
+            case 2: lean_phase2<2>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, false); break;
+            default: lean_phase2<3>(REV, rst_u32, kt_u32, bt, c0, offs, ro2, ko2, false); break;
         }
         fnext[0] = ex2(-((bt[frow] + bt[N + frow]) + (bt[2 * N + frow] + bt[3 * N + frow])));
         fnext[1] = ex2(-((bt[frow + 8] + bt[N + frow + 8]) + (bt[2 * N + frow + 8] + bt[3 * N + frow + 8])));

@@ -36,15 +36,31 @@ __device__ __forceinline__ constexpr int ktbase(bool REV, int I) {
                : (I == 0 ? 0 : I == 1 ? 2 * 1024 : I == 2 ? 6 * 1024 : I == 3 ? 12 * 1024 : 20 * 1024);
 }
 
-// phase 2 of one thread: cross-block factors -> Rst and the Ktil variants I+1..4 of this thread's 4 rows x 4 channels
+// phase 2 of one thread: cross-block factors -> Rst and the Ktil variants I+1..4 of this thread's 4 rows x 4 channels.
+// state_only (pass 1 of a time-segmented launch: no y): only the variant relative to the chunk end, the operand of dS.
 template <int I>
 __device__ __forceinline__ void lean_phase2(const bool REV, uint32_t rst_u32, uint32_t kt_u32, const float* bt, int c0, const int (&offs)[4],
-                                            const uint32_t (&ro2)[4][2], const uint32_t (&ko2)[4][2]) {
+                                            const uint32_t (&ro2)[4][2], const uint32_t (&ko2)[4][2], const bool state_only) {
     float tot[4][4];
 #pragma unroll
     for (int m = 0; m < 4; m++) {
         const float4 t = *reinterpret_cast<const float4*>(bt + m * N + c0);
         tot[m][0] = t.x; tot[m][1] = t.y; tot[m][2] = t.z; tot[m][3] = t.w;
+    }
+    if (state_only) {
+        float f[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            float s = 0.f;
+#pragma unroll
+            for (int m = I; m < 4; m++) s += tot[m][e];
+            f[e] = ex2(-s);                     // 2^(A_L - a_I)
+        }
+        const uint32_t f0 = pack_bf16(f[0], f[1]), f1 = pack_bf16(f[2], f[3]);
+        const uint32_t base = kt_u32 + ktbase(REV, 4);
+#pragma unroll
+        for (int r = 0; r < 4; r++) sts64(base + offs[r], bmul2(ko2[r][0], f0), bmul2(ko2[r][1], f1));
+        return;
     }
     if (I == 0) {
 #pragma unroll

@@ -764,7 +764,7 @@ int launch_fwd_scan(int dtype, const Params& p, cudaStream_t st) {
 // segment scan, pass 2.  Returns -1 when the launch does not qualify.
 int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
     Params q = p;
-    if (!plan_segments(q, scratch, scratch_bytes)) return -1;
+    if (!plan_segments(q, scratch, scratch_bytes, 4)) return -1;
     q.seg_mode = 1;
     int e = launch_fwd_scan(dtype, q, st);
     if (e) return e;

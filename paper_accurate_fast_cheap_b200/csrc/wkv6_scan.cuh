@@ -50,7 +50,7 @@ int launch_bwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_fwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05
 int launch_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* x_edge, const void* m, const void* const* maa, int reverse,
                     void* const* out, cudaStream_t st);
-bool plan_segments(Params& q, void* scratch, size_t scratch_bytes);
+bool plan_segments(Params& q, void* scratch, size_t scratch_bytes, int min_seg);
 int launch_seg_scan(const Params& q, cudaStream_t st);
 int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable

@@ -203,3 +203,22 @@ def test_time_segmented_fp32_scan(with_state):
         assert oracle.rel_err(got[2], sa) <= tol and oracle.rel_err(got[3], sb) <= tol
     print(f"fp32 scan, 8 sequences of T={T}: one CTA per sequence {t_plain:.3f} ms, time-segmented {t_seg:.3f} ms")
     assert t_seg < 0.6 * t_plain
+
+
+def test_time_segmented_two_segments_many_sequences():
+    """configs[2] at one GPU (8 utterances = 128 sequences): 2 segments per sequence (pass 1 is state-only, so two passes
+    over half the length still beat one CTA per sequence on 128 of 296 slots).  Parity as for every segmented launch."""
+    pk = _pk()
+    B, T, H = 8, 4200, 8
+    a = _inputs(B, T, H, torch.bfloat16, with_state=True, seed=71)
+    b = _inputs(B, T, H, torch.bfloat16, seed=72, layer=3)
+    ga, gb = _cuda(a), _cuda(b)
+    f, r_ = tuple(ga[n] for n in "rkvwu"), tuple(gb[n] for n in "rkvwu")
+    n0 = pk.launch_count()
+    y_f, y_b, s_f, s_b = pk.bi_forward_raw(f, r_, s0_f=ga["s0"], want_state=True)
+    assert pk.launch_count() - n0 == 3
+    ya, sa = oracle.fwd(a["r"], a["k"], a["v"], a["w"], a["u"], a["s0"], want_state=True, prec="f64")
+    yb, sb = oracle.fwd(b["r"], b["k"], b["v"], b["w"], b["u"], rev=True, want_state=True, prec="f64")
+    tol = TOL[torch.bfloat16]
+    assert oracle.rel_err(y_f, ya) <= tol and oracle.rel_err(y_b, yb) <= tol
+    assert oracle.rel_err(s_f, sa) <= tol and oracle.rel_err(s_b, sb) <= tol
