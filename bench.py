@@ -34,6 +34,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the fwd+bwd figures reported beside the inference line")
+    ap.add_argument("--no-longform", action="store_true", help="skip the configs[2] (T = 30 000) figure reported beside it")
     return ap.parse_args()
 
 
@@ -317,6 +318,46 @@ def run_b200(args):
                           "unit": "frames/s", "ms_per_step": tms, "steps": tsteps,
                           "roofline_bwd": roof("wkv6_bwd_chunk_kernel", bwd_bytes, tb, NCU_TRAFFIC["bwd"]),
                           "roofline_fwd_bwd": roof("forward + backward launches of one block", fwd_bytes + bwd_bytes, tf + tb)}
+
+    # ---- long-form (BASELINE configs[2]): 8 utterances of T = 30 000 frames in total, sharded by utterance over the
+    # ranks (8 / N per GPU: strong scaling), 12 blocks, both directions, forward; one input set per rank (2.4 GB per
+    # launch at B = 8: nothing stays in the 126 MB L2).  Few long sequences per GPU: the library runs them time-segmented
+    # on the scratch buffer lent here (wkv6_b200_set_scratch).
+    if not train and not args.no_longform and world <= 8:
+        LT, LB = 30000, max(1, 8 // world)
+        gl = torch.Generator(device=dev).manual_seed(777 + rank)
+        lsets = []
+        for _ in range(2):
+            t = [torch.randn(LB, LT, C, device=dev, generator=gl).to(dt) for _ in range(3)]
+            t.append((-6 + 5 * torch.rand(LB, LT, C, device=dev, generator=gl)).to(dt))
+            t.append((0.3 * torch.randn(H, 64, device=dev, generator=gl)).to(dt))
+            lsets.append(t)
+        ly = [torch.empty(LB, LT, C, device=dev, dtype=dt) for _ in range(2)]
+        scratch = torch.empty(6 << 20, device=dev, dtype=torch.uint8)
+        _lib.check(L.wkv6_b200_set_scratch(p(scratch), scratch.numel()))
+
+        def lstep():
+            f, b = lsets
+            for _ in range(NL):
+                _lib.check(L.wkv6_b200_bi_forward(0, LB, LT, C, H, p(f[0]), p(f[1]), p(f[2]), p(f[3]), p(f[4]), None, p(ly[0]), None,
+                                                  None, p(b[0]), p(b[1]), p(b[2]), p(b[3]), p(b[4]), None, p(ly[1]), None, None,
+                                                  flags, stream))
+
+        lstep(); lstep(); barrier()
+        n0 = pk.launch_count()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        lreps = 3
+        a0.record()
+        for _ in range(lreps):
+            lstep()
+        a1.record(); barrier()
+        lms = allmax(a0.elapsed_time(a1)) / lreps
+        extra["longform"] = {"metric": "encoder frames/s (bi-WKV6)", "value": world * LB * LT / (lms * 1e-3), "unit": "frames/s",
+                             "workload": f"configs[2]: 8 utterances x T=30000 in total, {LB} per GPU, C=512, 8 heads, bf16, 12 blocks, fwd",
+                             "scaling": "strong", "ms_per_step": lms, "steps": lreps,
+                             "launches_per_block": (pk.launch_count() - n0) // (lreps * NL)}
+        _lib.check(L.wkv6_b200_set_scratch(None, 0))
+        del lsets, ly, scratch
 
     # ---- end to end: pinned host inputs -> H2D -> op -> D2H of y, every step, through the C ABI
     e2e = None
