@@ -119,6 +119,27 @@ def config_dict(args, extra=None):
     return d
 
 
+_OUT_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: everything else a library may print there (NCCL's version banner, build
+    chatter) is sent to stderr for the whole run; emit() writes the line to the real stdout."""
+    global _OUT_FD
+    sys.stdout.flush()
+    _OUT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _OUT_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_OUT_FD, data)
+
+
 def run_reference(args):
     """Reference arm: the reference has no CPU WKV6 (model.py:105-106 is CUDA-only), so this times the oracle
     port of its kernels on all host cores.  Rank 0 only."""
@@ -148,7 +169,7 @@ def run_reference(args):
             "config": config_dict(args),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": th, "kind": "port", "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def make_layer_inputs(torch, dev, layer, dtype, train, pinned=False):
@@ -424,13 +445,14 @@ def run_b200(args):
                 "config": config_dict(args, {"algo": args.algo}), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": launches, "clocks": sampler.summary()}
         line.update(extra)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a = parse()
+    claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
