@@ -20,6 +20,13 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 static unsigned long long* g_dbg = nullptr;
 static void* g_scratch = nullptr;          // device scratch lent by the caller (wkv6_b200_set_scratch); never owned
 static size_t g_scratch_bytes = 0;
+static int g_scratch_device = -1;          // device the scratch lives on: launches on another device run unsegmented
+
+static void* scratch_for_current_device() {
+    int dev = -1;
+    if (!g_scratch || cudaGetDevice(&dev) != cudaSuccess || dev != g_scratch_device) return nullptr;
+    return g_scratch;
+}
 unsigned long long* debug_trace_buffer() { return g_dbg; }
 
 static int fail(int code, const char* fmt, ...) {
@@ -173,10 +180,10 @@ static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets
         if ((e = fill_fwd(p.d[i], dtype, B, T, C, sets[i], reverse[i], chunk ? 64 : TT, chunk))) return e;
     if (chunk) {
         // long sequences with few (batch, head) pairs: time-segmented two-pass forward on the lent scratch buffer
-        e = launch_fwd_chunk_segmented(p, g_scratch, g_scratch_bytes, (cudaStream_t)stream);
+        e = launch_fwd_chunk_segmented(p, scratch_for_current_device(), g_scratch_bytes, (cudaStream_t)stream);
         if (e < 0) e = launch_fwd_chunk(p, (cudaStream_t)stream);
     } else {
-        e = launch_fwd_scan_segmented(dtype, p, g_scratch, g_scratch_bytes, (cudaStream_t)stream);
+        e = launch_fwd_scan_segmented(dtype, p, scratch_for_current_device(), g_scratch_bytes, (cudaStream_t)stream);
         if (e < 0) e = launch_fwd_scan(dtype, p, (cudaStream_t)stream);
     }
     return cuda_fail(e, "wkv6 forward launch");
@@ -308,8 +315,18 @@ int wkv6_b200_debug_trace(int enable, unsigned long long* out) {
  * library never allocates or frees it; it is used by forward calls on whatever stream they run (one stream at a time). */
 int wkv6_b200_set_scratch(void* device_ptr, size_t bytes) {
     if (device_ptr && !aligned16(device_ptr)) return fail(WKV6_E_BADARG, "set_scratch: misaligned pointer");
+    int dev = -1;
+    if (device_ptr) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, device_ptr) != cudaSuccess || at.type != cudaMemoryTypeDevice) {
+            cudaGetLastError();
+            return fail(WKV6_E_BADARG, "set_scratch: not a device pointer");
+        }
+        dev = at.device;
+    }
     g_scratch = device_ptr;
     g_scratch_bytes = device_ptr ? bytes : 0;
+    g_scratch_device = dev;
     return 0;
 }
 int wkv6_b200_debug_trace_ctas(unsigned long long* out) {

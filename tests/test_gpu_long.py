@@ -222,3 +222,13 @@ def test_time_segmented_two_segments_many_sequences():
     tol = TOL[torch.bfloat16]
     assert oracle.rel_err(y_f, ya) <= tol and oracle.rel_err(y_b, yb) <= tol
     assert oracle.rel_err(s_f, sa) <= tol and oracle.rel_err(s_b, sb) <= tol
+
+
+def test_set_scratch_rejects_host_memory():
+    """The scratch must be device memory (the library records which device it lives on and segments only launches on
+    that device)."""
+    from paper_accurate_fast_cheap_b200 import _lib
+    host = torch.empty(1 << 20, dtype=torch.uint8)
+    with pytest.raises(_lib.Wkv6Error):
+        _lib.check(_lib.lib().wkv6_b200_set_scratch(host.data_ptr(), host.numel()))
+    _lib.check(_lib.lib().wkv6_b200_set_scratch(None, 0))
