@@ -13,45 +13,17 @@
 // vector, consecutive threads touch consecutive vectors of a row.
 //
 // Bit-exact with the reference's eager ops: every intermediate the reference materialises is rounded to the I/O type
-// here too (bf16: sub, add, mul, add each round once, as ATen's bf16 elementwise kernels do; fp32: plain IEEE ops, no
-// FMA contraction).
+// here too (bf16: packed sub / add / mul, one rounding per operation like ATen's bf16 elementwise kernels; fp32: plain
+// IEEE ops, no FMA contraction).
 #include "wkv6_scan.cuh"
-#include "wkv6_umma.cuh"
 
 namespace wkv6 {
 
 namespace {
 
 template <typename T> struct Vec;
-template <> struct Vec<__nv_bfloat16> {
-    static constexpr int W = 8;   // elements per 16-byte vector
-    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&f)[8]) { unpack(*reinterpret_cast<const uint4*>(p), f); }
-    static __device__ __forceinline__ void unpack(const uint4 q, float (&f)[8]) {
-        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            f[2 * i] = __uint_as_float(w[i] << 16);
-            f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
-        }
-    }
-    static __device__ __forceinline__ void store(__nv_bfloat16* p, const float (&f)[8]) {
-        uint4 q;
-        q.x = pack_bf16(f[0], f[1]); q.y = pack_bf16(f[2], f[3]); q.z = pack_bf16(f[4], f[5]); q.w = pack_bf16(f[6], f[7]);
-        *reinterpret_cast<uint4*>(p) = q;
-    }
-    static __device__ __forceinline__ float rnd(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
-};
-template <> struct Vec<float> {
-    static constexpr int W = 4;
-    static __device__ __forceinline__ void load(const float* p, float (&f)[4]) { unpack(*reinterpret_cast<const uint4*>(p), f); }
-    static __device__ __forceinline__ void unpack(const uint4 q, float (&f)[4]) {
-        f[0] = __uint_as_float(q.x); f[1] = __uint_as_float(q.y); f[2] = __uint_as_float(q.z); f[3] = __uint_as_float(q.w);
-    }
-    static __device__ __forceinline__ void store(float* p, const float (&f)[4]) {
-        *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
-    }
-    static __device__ __forceinline__ float rnd(float v) { return v; }
-};
+template <> struct Vec<__nv_bfloat16> { static constexpr int W = 8; };   // elements per 16-byte vector
+template <> struct Vec<float> { static constexpr int W = 4; };
 
 struct TmixArgs {
     const void* x;
@@ -63,54 +35,66 @@ struct TmixArgs {
     int T, C, reverse;
 };
 
+// One 16-byte vector of the elementwise chain.  bf16: packed bf16x2 instructions (sub / add / mul round to nearest even
+// once per operation, which is what the eager ops produce: ATen computes each op in fp32 and rounds the result to bf16, and
+// for bf16 operands the fp32 intermediate is exact or far from a bf16 tie, so the two roundings agree); fp32: plain IEEE
+// operations without FMA contraction.
+template <typename T> struct Ops;
+template <> struct Ops<__nv_bfloat16> {
+    using V = uint4;
+    static __device__ __forceinline__ uint32_t sub2(uint32_t a, uint32_t b) { uint32_t d; asm("sub.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+    static __device__ __forceinline__ uint32_t add2(uint32_t a, uint32_t b) { uint32_t d; asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+    static __device__ __forceinline__ uint32_t mul2(uint32_t a, uint32_t b) { uint32_t d; asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+    static __device__ __forceinline__ V zero() { return make_uint4(0, 0, 0, 0); }
+    static __device__ __forceinline__ V sub(V a, V b) { return make_uint4(sub2(a.x, b.x), sub2(a.y, b.y), sub2(a.z, b.z), sub2(a.w, b.w)); }
+    static __device__ __forceinline__ V add(V a, V b) { return make_uint4(add2(a.x, b.x), add2(a.y, b.y), add2(a.z, b.z), add2(a.w, b.w)); }
+    static __device__ __forceinline__ V mul(V a, V b) { return make_uint4(mul2(a.x, b.x), mul2(a.y, b.y), mul2(a.z, b.z), mul2(a.w, b.w)); }
+};
+template <> struct Ops<float> {
+    using V = float4;
+    static __device__ __forceinline__ V zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+    static __device__ __forceinline__ V sub(V a, V b) { return make_float4(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y), __fsub_rn(a.z, b.z), __fsub_rn(a.w, b.w)); }
+    static __device__ __forceinline__ V add(V a, V b) { return make_float4(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z), __fadd_rn(a.w, b.w)); }
+    static __device__ __forceinline__ V mul(V a, V b) { return make_float4(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y), __fmul_rn(a.z, b.z), __fmul_rn(a.w, b.w)); }
+};
+
+// Thread block = (vx, vy): vx threads along the vectors of a row, vy rows; grid-stride over row groups.  One 32-bit
+// modulo per thread and row (t = row % T), no other index arithmetic.
 template <typename T, bool STAGE2>
 __global__ void __launch_bounds__(256) wkv6_tmix_mix_kernel(const TmixArgs a) {
+    using O = Ops<T>;
+    using V = typename O::V;
     constexpr int W = Vec<T>::W;
     const int vpr = a.C / W;                                   // vectors per row
-    const unsigned nvec = (unsigned)(a.rows * vpr);            // < 2^31, checked by the launcher: 32-bit index arithmetic
     const T* x = static_cast<const T*>(a.x);
-    for (unsigned v = blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += gridDim.x * blockDim.x) {
-        const unsigned row = v / (unsigned)vpr;
-        const int c = (int)(v - row * vpr) * W;
-        const int t = (int)(row % (unsigned)a.T);
-        const size_t off = (size_t)row * a.C + c;
-        float xv[W], xs[W], xx[W];
-        Vec<T>::load(x + off, xv);
+    const size_t plane = (size_t)a.rows * a.C;
+    for (long long row = (long long)blockIdx.x * blockDim.y + threadIdx.y; row < a.rows; row += (long long)gridDim.x * blockDim.y) {
+        const int t = (int)((unsigned long long)row % (unsigned)a.T);
         const bool edge = a.reverse ? (t == a.T - 1) : (t == 0);
-        if (edge) {
-            if (a.x_edge) {
-                Vec<T>::load(static_cast<const T*>(a.x_edge) + (size_t)(row / (unsigned)a.T) * a.C + c, xs);
+        for (int vi = threadIdx.x; vi < vpr; vi += blockDim.x) {
+            const int c = vi * W;
+            const size_t off = (size_t)row * a.C + c;
+            const V xv = *reinterpret_cast<const V*>(x + off);
+            V xs;
+            if (!edge) xs = *reinterpret_cast<const V*>(a.reverse ? x + off + a.C : x + off - a.C);
+            else if (a.x_edge) xs = *reinterpret_cast<const V*>(static_cast<const T*>(a.x_edge) + (size_t)(row / a.T) * a.C + c);
+            else xs = O::zero();
+            if (!STAGE2) {
+                const V mx = *reinterpret_cast<const V*>(static_cast<const T*>(a.maa[0]) + c);
+                *reinterpret_cast<V*>(static_cast<T*>(a.out[0]) + off) = O::add(xv, O::mul(O::sub(xs, xv), mx));
             } else {
+                V qm[4];   // the four m_c vectors are read once: streaming loads, all in flight before the first use
 #pragma unroll
-                for (int i = 0; i < W; i++) xs[i] = 0.f;
-            }
-        } else {
-            Vec<T>::load(a.reverse ? x + off + a.C : x + off - a.C, xs);
-        }
-#pragma unroll
-        for (int i = 0; i < W; i++) xx[i] = Vec<T>::rnd(__fsub_rn(xs[i], xv[i]));
-        if (!STAGE2) {
-            float mx[W], o[W];
-            Vec<T>::load(static_cast<const T*>(a.maa[0]) + c, mx);
-#pragma unroll
-            for (int i = 0; i < W; i++) o[i] = Vec<T>::rnd(__fadd_rn(xv[i], Vec<T>::rnd(__fmul_rn(xx[i], mx[i]))));
-            Vec<T>::store(static_cast<T*>(a.out[0]) + off, o);
-        } else {
-            const size_t plane = (size_t)a.rows * a.C;
-            uint4 qm[4];   // the four m_c vectors are read once: streaming loads, all in flight before the first use
-#pragma unroll
-            for (int k = 0; k < 4; k++) qm[k] = __ldcs(reinterpret_cast<const uint4*>(static_cast<const T*>(a.m) + k * plane + off));
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                float mk[W], mm[W], o[W];
-                Vec<T>::load(static_cast<const T*>(a.maa[k + 1]) + c, mk);
-                Vec<T>::unpack(qm[k], mm);
-#pragma unroll
-                for (int i = 0; i < W; i++) {
-                    const float s = Vec<T>::rnd(__fadd_rn(mk[i], mm[i]));
-                    o[i] = Vec<T>::rnd(__fadd_rn(xv[i], Vec<T>::rnd(__fmul_rn(xx[i], s))));
+                for (int k = 0; k < 4; k++) {
+                    const uint4 q = __ldcs(reinterpret_cast<const uint4*>(static_cast<const T*>(a.m) + k * plane + off));
+                    qm[k] = *reinterpret_cast<const V*>(&q);
                 }
-                Vec<T>::store(static_cast<T*>(a.out[k]) + off, o);
+                const V xx = O::sub(xs, xv);
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const V mk = *reinterpret_cast<const V*>(static_cast<const T*>(a.maa[k + 1]) + c);
+                    *reinterpret_cast<V*>(static_cast<T*>(a.out[k]) + off) = O::add(xv, O::mul(xx, O::add(mk, qm[k])));
+                }
             }
         }
     }
@@ -118,13 +102,14 @@ __global__ void __launch_bounds__(256) wkv6_tmix_mix_kernel(const TmixArgs a) {
 
 template <typename T, bool STAGE2>
 int launch_t(const TmixArgs& a, cudaStream_t st) {
-    const long long nvec = a.rows * (a.C / Vec<T>::W);
-    if (nvec == 0) return 0;
-    if (nvec >= (1ll << 31)) return (int)cudaErrorInvalidValue;
-    // up to 148 SMs x 8 resident CTAs x 4 waves of 256 threads, grid-stride beyond that
-    long long blocks = (nvec + 255) / 256;
-    if (blocks > 148 * 32) blocks = 148 * 32;
-    wkv6_tmix_mix_kernel<T, STAGE2><<<dim3((unsigned)blocks), dim3(256), 0, st>>>(a);
+    if (a.rows == 0) return 0;
+    const int vpr = a.C / Vec<T>::W;
+    int vx = 32;
+    while (vx < vpr && vx < 256) vx <<= 1;
+    const int vy = 256 / vx;
+    long long blocks = (a.rows + vy - 1) / vy;
+    if (blocks > 148 * 32) blocks = 148 * 32;   // up to 148 SMs x 8 resident CTAs x 4 waves, grid-stride beyond that
+    wkv6_tmix_mix_kernel<T, STAGE2><<<dim3((unsigned)blocks), dim3(vx, vy), 0, st>>>(a);
     count_launch(1);
     return (int)cudaGetLastError();
 }

@@ -25,18 +25,22 @@ out1 = [torch.empty_like(xs[0]) for _ in range(NL)]
 out2 = [[torch.empty_like(xs[0]) for _ in range(4)] for _ in range(NL)]
 L = _lib.lib()
 p = lambda t: ctypes.c_void_p(t.data_ptr())
-st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+
+def st_now():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
 def fused1():
     for l in range(NL):
-        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), None, None, p(maa[0]), None, None, None, None, 0, p(out1[l]), None, None, None, None, st))
+        _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), None, None, p(maa[0]), None, None, None, None, 0, p(out1[l]), None, None, None, None, st_now()))
 
 
 def fused2():
     for l in range(NL):
         _lib.check(L.wkv6_b200_tmix_mix(0, B, T, C, p(xs[l]), None, p(ms[l]), None, p(maa[1]), p(maa[2]), p(maa[3]), p(maa[4]), 0, None,
-                                        *[p(o) for o in out2[l]], st))
+                                        *[p(o) for o in out2[l]], st_now()))
 
 
 def eager1():
@@ -50,16 +54,27 @@ def eager2():
 
 
 def timed(fn, reps=20):
-    for _ in range(3):
+    """us per block.  The 12 launches of a pass are captured in a CUDA graph and the graph is replayed: a stage-1 launch
+    is ~5 us of GPU work, less than the ~10 us a ctypes call costs on the host, so timing eager launches would time Python."""
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            fn()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
         fn()
+    g.replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(reps):
-        fn()
+        g.replay()
     e1.record()
     torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / (reps * NL) * 1e3      # us per launch / per block
+    return e0.elapsed_time(e1) / (reps * NL) * 1e3
 
 
 peak = 6449.4
@@ -69,7 +84,10 @@ except Exception:
     pass
 n = B * T * C * 2
 res = {}
+only = os.environ.get("TMIX_ONLY")          # e.g. stage2_fused: the one variant an ncu capture wants
 for name, fn, passes in (("stage1_fused", fused1, 2), ("stage1_eager", eager1, 2), ("stage2_fused", fused2, 9), ("stage2_eager", eager2, 9)):
+    if only and name != only:
+        continue
     us = timed(fn)
     res[name] = {"us_per_block": us, "algorithmic_GBps": passes * n / us / 1e3, "frac_of_hbm_peak": passes * n / us / 1e3 / peak}
 print(json.dumps({"workload": "tmix token-shift + maa mixes, B=16 x T=750 x C=512 bf16, 12 distinct blocks", "hbm_peak_GBps": peak, **res}))
