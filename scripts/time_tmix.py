@@ -84,8 +84,25 @@ except Exception:
     pass
 n = B * T * C * 2
 res = {}
+# row a7: (y_f + y_b) / 2 -> fp32 (rwkv_wrapper_bidirectional.py:48-56): 2 bf16 reads + 1 fp32 write = 8 bytes per element
+ya = [torch.randn(B, T, C, device=dev, generator=g).to(dt) for _ in range(NL)]
+yb = [torch.randn(B, T, C, device=dev, generator=g).to(dt) for _ in range(NL)]
+yo = [torch.empty(B, T, C, device=dev, dtype=torch.float32) for _ in range(NL)]
+
+
+def combine_fused():
+    for l in range(NL):
+        _lib.check(L.wkv6_b200_combine(0, ya[l].numel(), p(ya[l]), p(yb[l]), ctypes.c_float(0.5), 1, p(yo[l]), st_now()))
+
+
+def combine_eager():
+    for l in range(NL):
+        ((ya[l] + yb[l]) / 2).float()
+
+
 only = os.environ.get("TMIX_ONLY")          # e.g. stage2_fused: the one variant an ncu capture wants
-for name, fn, passes in (("stage1_fused", fused1, 2), ("stage1_eager", eager1, 2), ("stage2_fused", fused2, 9), ("stage2_eager", eager2, 9)):
+for name, fn, passes in (("stage1_fused", fused1, 2), ("stage1_eager", eager1, 2), ("stage2_fused", fused2, 9), ("stage2_eager", eager2, 9),
+                         ("combine_fused", combine_fused, 4), ("combine_eager", combine_eager, 4)):
     if only and name != only:
         continue
     us = timed(fn)
