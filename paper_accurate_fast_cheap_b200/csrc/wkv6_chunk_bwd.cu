@@ -106,6 +106,22 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
         tma_prefetch_desc(&D.mg); tma_prefetch_desc(&D.mc);
         tma_prefetch_desc(&D.mgr); tma_prefetch_desc(&D.mgk); tma_prefetch_desc(&D.mgv); tma_prefetch_desc(&D.mgw);
+        // the first chunk's loads go out here, before the rest of the prologue (TMEM allocation, shared-memory clears,
+        // reverse-state load), not after it
+        fence_proxy_async();
+        pdl_wait();
+        if (nchunks > 0) {
+            const int q0 = rev ? 0 : nchunks - 1;          // tile of the chunk the reverse sweep starts with
+            mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
+            tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q0 * CL, b);
+            tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q0 * CL, b);
+            tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q0 * CL, b);
+            mbar_arrive_expect_tx(&sm.bar_vg[0], 2u * CL * 128);
+            tma_load_3d(sm.v[0], &D.mv, &sm.bar_vg[0], h * N, q0 * CL, b);
+            tma_load_3d(sm.g[0], &D.mg, &sm.bar_vg[0], h * N, q0 * CL, b);
+            mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
+            tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1)) * N);
+        }
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
@@ -208,7 +224,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
         tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1 - cb)) * N);
     };
-    if (tid == 0 && nchunks > 0) { issue_rkw(0); issue_vg(0); issue_sp(0); }
+    // (the loads of the first chunk were issued at the top of the prologue)
 
     constexpr uint32_t ID_KK64 = umma_idesc(0, 0, 64, 64);
     constexpr uint32_t ID_KK16 = umma_idesc(0, 0, 64, 16);

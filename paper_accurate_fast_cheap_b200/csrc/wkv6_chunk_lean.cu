@@ -57,18 +57,33 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
 #define TMA_THR (warp == 5 && elect_one())
 
     if (tid == 0) {
-        mbar_init(&sm.bar_rkw, 1);
-        mbar_init(&sm.bar_v[0], 1);
-        mbar_init(&sm.bar_v[1], 1);
         mbar_init(&sm.bar_p, 4);      // the four G1 groups are issued by four warps' lane 0 in parallel
         mbar_init(&sm.bar_s, 1);
         mbar_init(&sm.bar_y, 1);
         fence_barrier_init();
     }
     if (TMA_THR) {
+        // the TMA lane owns the load barriers: it initialises them and puts the first chunk's loads in flight before the
+        // rest of the prologue (TMEM allocation, shared-memory clears, state load) instead of after it
+        mbar_init(&sm.bar_rkw, 1);
+        mbar_init(&sm.bar_v[0], 1);
+        mbar_init(&sm.bar_v[1], 1);
+        fence_barrier_init();
+        fence_proxy_async();
         tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mk); tma_prefetch_desc(&D.mv); tma_prefetch_desc(&D.mw);
         if (!skip_y) tma_prefetch_desc(&D.my);
+        pdl_wait();
+        if (nchunks > 0) {
+            const int q = tileq(0);
+            mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
+            tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q * CL, b);
+            tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q * CL, b);
+            tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q * CL, b);
+            mbar_arrive_expect_tx(&sm.bar_v[0], (uint32_t)CL * 128);
+            tma_load_3d(sm.v[0], &D.mv, &sm.bar_v[0], h * N, q * CL, b);
+        }
     }
+    __syncwarp();
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -295,8 +310,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
     };
 
     if (nchunks > 0) {
-        if (TMA_THR) { issue_rkw(0); issue_v(0); }
-        phase1(0);
+        phase1(0);                    // the loads of chunk 0 were issued at the top of the prologue
         __syncthreads();
         if (TMA_THR && nchunks > 1) { issue_rkw(1); issue_v(1); }
         phase2(0);
