@@ -175,6 +175,9 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
     constexpr uint32_t ID_G3 = umma_idesc(0, 1, 64, 64);
 
     uint32_t ro2[4][2], ko2[4][2];   // Rtil / Ktil(own) of this thread's 4 rows x 4 channels, packed bf16x2
+    // state-only mode (pass 1 of a time-segmented launch): no y, so no P^T (G1), no G2 / G3, no bonus and no R-side tiles;
+    // what is left per chunk is the decays, Ktil relative to the chunk end, dS (G4) and the state update
+    const bool so = decay_out != nullptr && skip_y && !ckpt_on;
 
     // ---- phase 1 of chunk c: decays, in-block cumulative sums, Rtil, Ktil(own block), bonus
     auto phase1 = [&](const int c) {
@@ -206,6 +209,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             }
         }
         // bonus sum_j r u k over this thread's 4 channels (packed bf16), then a transposing reduction over the 8 lanes
+        if (!so) {
         float bs[4];
 #pragma unroll
         for (int r = 0; r < 4; r++) {
@@ -228,6 +232,7 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
                 sm.bonus[ch][REV ? 63 - pos : pos] = kk_;
             }
         }
+        }   // !so
 #pragma unroll
         for (int e = 0; e < 4; e++) {   // inclusive sums over this thread's 4 steps
             m[1][e] += m[0][e];
@@ -251,22 +256,24 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             float fr[4], fk[4];
 #pragma unroll
             for (int e = 0; e < 4; e++) {
-                const float aex = r ? excl[e] + m[r - 1][e] : excl[e];          // -(A_p  - a_I) >= 0
                 const float ain = r == 3 ? m[3][e] : excl[e] + m[r][e];         // -(A+_p - a_I) >= 0
-                fr[e] = ex2(-aex);
                 fk[e] = ex2(ain);
             }
-            ro2[r][0] = bmul2(rr[r][0], pack_bf16(fr[0], fr[1]));
-            ro2[r][1] = bmul2(rr[r][1], pack_bf16(fr[2], fr[3]));
             ko2[r][0] = bmul2(kk[r][0], pack_bf16(fk[0], fk[1]));
             ko2[r][1] = bmul2(kk[r][1], pack_bf16(fk[2], fk[3]));
-            sts64(roff_u32 + offs[r], ro2[r][0], ro2[r][1]);
-            sts64(kt_u32 + vb_own + offs[r], ko2[r][0], ko2[r][1]);
+            if (!so) {
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float aex = r ? excl[e] + m[r - 1][e] : excl[e];      // -(A_p  - a_I) >= 0
+                    fr[e] = ex2(-aex);
+                }
+                ro2[r][0] = bmul2(rr[r][0], pack_bf16(fr[0], fr[1]));
+                ro2[r][1] = bmul2(rr[r][1], pack_bf16(fr[2], fr[3]));
+                sts64(roff_u32 + offs[r], ro2[r][0], ro2[r][1]);
+                sts64(kt_u32 + vb_own + offs[r], ko2[r][0], ko2[r][1]);   // Ktil(own): operand of G1 only
+            }
         }
     };
-    // state-only mode (pass 1 of a time-segmented launch): no y, so no P^T (G1), no G2 / G3 and no R-side tiles; what is
-    // left per chunk is the decays, Ktil relative to the chunk end, dS (G4) and the state update -- under half the work
-    const bool so = decay_out != nullptr && skip_y && !ckpt_on;
     auto phase2 = [&](const int c) {
         const float* bt = &sm.blocktot[c & 1][0][0];
         switch (I) {   // warp-uniform
