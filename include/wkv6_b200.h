@@ -29,6 +29,10 @@
  *     natural (un-flipped) position: identical to flip -> scan -> flip over the padded time
  *     axis, without the copies.
  *   - `stream` is a cudaStream_t (NULL = legacy default stream).  Calls are asynchronous.
+ *   - The library keeps no per-call state between entry points: every buffer a launch uses (outputs, checkpoints,
+ *     backward workspace, forward scratch) is an argument, so concurrent calls on different streams / devices / host
+ *     threads are independent.  Process-wide: the launch counter, the bf16 arithmetic selector (wkv6_b200_set_algo)
+ *     and the debug trace buffer.
  *   - Return value: 0 on success, a negative WKV6_E_* code for rejected arguments,
  *     a positive cudaError_t for CUDA failures.  wkv6_b200_last_error() gives the text.
  *   - No CPU fallback exists: without a CUDA device every compute entry point fails.
@@ -56,7 +60,9 @@ extern "C" {
 #define WKV6_BI_L2R      1     /* run the left-to-right direction (set "f")                   */
 #define WKV6_BI_R2L      2     /* run the right-to-left direction (set "b"), flip-free        */
 
-/* kernel selection for forward (bf16 only; f32 always uses the exact scan) */
+/* Arithmetic selector for bf16 I/O (f32 I/O always uses the exact scan): AUTO = CHUNK = the tcgen05 chunk kernels (the
+ * only bf16 production path); SCAN = the exact fp32-math recurrence on bf16 I/O, a documented numerics option (it is the
+ * fp32 kernel instantiated for bf16 tensors, not a second implementation of the chunk path). */
 #define WKV6_ALGO_AUTO   0
 #define WKV6_ALGO_SCAN   1     /* fp32 recurrent scan on the FMA pipe (exact form)            */
 #define WKV6_ALGO_CHUNK  2     /* chunked dense-contraction form on tcgen05/TMEM              */
@@ -65,10 +71,6 @@ int  wkv6_b200_abi_version(void);
 const char* wkv6_b200_last_error(void);
 /* Number of kernels this library has launched since load (the bench's gpu_launches). */
 long long wkv6_b200_launch_count(void);
-/* Optional: lend a device scratch buffer (caller-owned, >= 16-byte aligned) to the library.  With it, forward calls
- * (either dtype) whose sequences are long (>= 2048 steps) and few (directions * B * H <= 148 for bf16, <= 74 for f32) run
- * time-segmented (two passes over 2..37 segments per sequence) instead of one CTA per sequence; 5 MB covers every case.  NULL / 0 takes it back. */
-int  wkv6_b200_set_scratch(void* device_ptr, size_t bytes);
 /* Debug aid: clock64() trace of one CTA of the chunk kernels (see csrc/wkv6_capi.cu); not part of the data path. */
 int  wkv6_b200_debug_trace(int enable, unsigned long long* out);
 int  wkv6_b200_debug_trace_ctas(unsigned long long* out);   /* 4*1024 entries: per-CTA {t_start, smid, t_end, 0} */
@@ -81,9 +83,19 @@ int  wkv6_b200_get_algo(void);
  * and backward launches (model.py:131,149), so NULL is always accepted. */
 size_t wkv6_b200_checkpoint_bytes(int B, int T, int C, int H);
 
+/* Time segmentation of the forward (optional).  One CTA per (direction, batch, head) leaves most of the 148 SMs idle when
+ * a GPU holds few, long sequences (directions * B * H <= 148 for bf16, <= 74 for f32; T >= 2048: one to eight 5-minute
+ * utterances, a 1-hour utterance).  Given `scratch` (device memory, caller-owned, 16-byte aligned, used only by this call
+ * on `stream`) of at least wkv6_b200_forward_scratch_bytes(...) bytes, such a forward runs in 2..40 time segments per
+ * sequence over all SMs (three launches: local states, segment scan, outputs); same results to the dtype's tolerance.
+ * The function returns 0 for shapes that would not be segmented; scratch == NULL always means one CTA per sequence.
+ * The reference has no counterpart: it runs one thread block per (batch, head) whatever T is (wkv6_cuda.cu:269). */
+size_t wkv6_b200_forward_scratch_bytes(int dtype, int B, int T, int C, int H, int ndirections);
+
 int wkv6_b200_forward(int dtype, int B, int T, int C, int H,
                       const void* r, const void* k, const void* v, const void* w, const void* u,
-                      const float* s0, void* y, float* sT, void* ckpt, int reverse, void* stream);
+                      const float* s0, void* y, float* sT, void* ckpt, int reverse,
+                      void* scratch, size_t scratch_bytes, void* stream);
 
 /* Bytes of scratch the backward entry points need (0 is possible). */
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections);
@@ -102,7 +114,7 @@ int wkv6_b200_bi_forward(int dtype, int B, int T, int C, int H,
                          const float* s0_f, void* y_f, float* sT_f, void* ckpt_f,
                          const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
                          const float* s0_b, void* y_b, float* sT_b, void* ckpt_b,
-                         int flags, void* stream);
+                         int flags, void* scratch, size_t scratch_bytes, void* stream);
 
 int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,
                           const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,

@@ -17,16 +17,7 @@ static std::atomic<int> g_algo{WKV6_ALGO_AUTO};
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
-static unsigned long long* g_dbg = nullptr;
-static void* g_scratch = nullptr;          // device scratch lent by the caller (wkv6_b200_set_scratch); never owned
-static size_t g_scratch_bytes = 0;
-static int g_scratch_device = -1;          // device the scratch lives on: launches on another device run unsegmented
-
-static void* scratch_for_current_device() {
-    int dev = -1;
-    if (!g_scratch || cudaGetDevice(&dev) != cudaSuccess || dev != g_scratch_device) return nullptr;
-    return g_scratch;
-}
+static unsigned long long* g_dbg = nullptr;    // debug aid only (wkv6_b200_debug_trace), never on the data path
 unsigned long long* debug_trace_buffer() { return g_dbg; }
 
 static int fail(int code, const char* fmt, ...) {
@@ -60,14 +51,48 @@ static encode_fn_t get_encode() {
     return fn;
 }
 
-// 3-D view [B][T][C] of a contiguous tensor, box = [1][rows][64 channels]
-static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, int C, int rows, bool swizzle128 = false) {
-    encode_fn_t enc = get_encode();
-    if (!enc) return fail(WKV6_E_NODRIVER, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+// Encoded tensor maps are pure functions of (pointer, shape, box, swizzle): a small per-thread direct-mapped cache saves
+// the 10 (forward) / 22 (backward) cuTensorMapEncodeTiled driver calls of a bidirectional launch whenever a caller comes
+// back with the same buffers (the caching allocator of PyTorch hands the same blocks out step after step).
+struct MapKey {
+    const void* ptr;
+    int kind, B, T, C, rows, swz;
+    bool operator==(const MapKey& o) const {
+        return ptr == o.ptr && kind == o.kind && B == o.B && T == o.T && C == o.C && rows == o.rows && swz == o.swz;
+    }
+};
+struct MapSlot {
+    MapKey key;
+    CUtensorMap map;
+    bool valid;
+};
+constexpr int kMapSlots = 256;
+static MapSlot* map_cache() {
+    static thread_local MapSlot slots[kMapSlots];   // zero-initialised: valid = false
+    return slots;
+}
+static unsigned map_hash(const MapKey& k) {
+    unsigned long long h = reinterpret_cast<uintptr_t>(k.ptr) >> 4;
+    h = h * 0x9E3779B97F4A7C15ull ^ ((unsigned long long)k.T * 131u + (unsigned)k.B * 31u + (unsigned)k.C + (unsigned)k.rows * 7u +
+                                     (unsigned)k.kind * 3u + (unsigned)k.swz);
+    return (unsigned)(h >> 40) & (kMapSlots - 1);
+}
+
+static void bind_context_once() {
     // cuTensorMapEncodeTiled wants a current context; threads that never touched the runtime (autograd workers)
     // have none until a runtime call binds the primary context.
     static thread_local bool ctx_bound = false;
     if (!ctx_bound) { cudaFree(nullptr); ctx_bound = true; }
+}
+
+// 3-D view [B][T][C] of a contiguous tensor, box = [1][rows][64 channels]
+static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, int C, int rows, bool swizzle128 = false) {
+    const MapKey key = {ptr, dtype, B, T, C, rows, swizzle128 ? 1 : 0};
+    MapSlot& slot = map_cache()[map_hash(key)];
+    if (slot.valid && slot.key == key) { *m = slot.map; return 0; }
+    encode_fn_t enc = get_encode();
+    if (!enc) return fail(WKV6_E_NODRIVER, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    bind_context_once();
     const size_t es = dtype == WKV6_DTYPE_BF16 ? 2 : 4;
     const cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)T, (cuuint64_t)B};
     const cuuint64_t strides[2] = {(cuuint64_t)C * es, (cuuint64_t)T * C * es};
@@ -79,13 +104,18 @@ static int make_map(CUtensorMap* m, int dtype, const void* ptr, int B, int T, in
                            CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(WKV6_E_BADARG, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    slot.key = key; slot.map = *m; slot.valid = true;
     return 0;
 }
 
 // chunk-start state checkpoints: [B*H*nchunks*64 rows][64] bf16, box 64 x 64, 128B swizzle
 static int make_ckpt_map(CUtensorMap* m, const void* ptr, int B, int T, int H) {
+    const MapKey key = {ptr, 100, B, T, H, 64, 1};
+    MapSlot& slot = map_cache()[map_hash(key)];
+    if (slot.valid && slot.key == key) { *m = slot.map; return 0; }
     encode_fn_t enc = get_encode();
     if (!enc) return fail(WKV6_E_NODRIVER, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    bind_context_once();
     const int nchunks = (T + 63) / 64;
     const cuuint64_t dims[2] = {64u, (cuuint64_t)B * H * nchunks * 64};
     const cuuint64_t strides[1] = {128u};
@@ -95,6 +125,7 @@ static int make_ckpt_map(CUtensorMap* m, const void* ptr, int B, int T, int H) {
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(WKV6_E_BADARG, "cuTensorMapEncodeTiled(ckpt) failed with CUresult %d", (int)r);
+    slot.key = key; slot.map = *m; slot.valid = true;
     return 0;
 }
 
@@ -158,7 +189,8 @@ static int fill_fwd(DirArgs& d, int dtype, int B, int T, int C, const FwdSet& s,
     return 0;
 }
 
-static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets, const int* reverse, int nset, void* stream) {
+static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets, const int* reverse, int nset,
+                       void* scratch, size_t scratch_bytes, void* stream) {
     int e = check_common(dtype, B, T, C, H);
     if (e) return e;
     if (nset == 0 || B == 0) return 0;
@@ -176,14 +208,15 @@ static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets
         return 0;
     }
     const bool chunk = use_chunk(dtype, T);
+    if (scratch && !aligned16(scratch)) return fail(WKV6_E_BADARG, "forward: misaligned scratch buffer");
     for (int i = 0; i < nset; i++)
         if ((e = fill_fwd(p.d[i], dtype, B, T, C, sets[i], reverse[i], chunk ? 64 : TT, chunk))) return e;
     if (chunk) {
-        // long sequences with few (batch, head) pairs: time-segmented two-pass forward on the lent scratch buffer
-        e = launch_fwd_chunk_segmented(p, scratch_for_current_device(), g_scratch_bytes, (cudaStream_t)stream);
+        // long sequences with few (batch, head) pairs: time-segmented two-pass forward on the caller's scratch buffer
+        e = launch_fwd_chunk_segmented(p, scratch, scratch_bytes, (cudaStream_t)stream);
         if (e < 0) e = launch_fwd_chunk(p, (cudaStream_t)stream);
     } else {
-        e = launch_fwd_scan_segmented(dtype, p, scratch_for_current_device(), g_scratch_bytes, (cudaStream_t)stream);
+        e = launch_fwd_scan_segmented(dtype, p, scratch, scratch_bytes, (cudaStream_t)stream);
         if (e < 0) e = launch_fwd_scan(dtype, p, (cudaStream_t)stream);
     }
     return cuda_fail(e, "wkv6 forward launch");
@@ -297,7 +330,7 @@ using namespace wkv6;
 
 extern "C" {
 
-int wkv6_b200_abi_version(void) { return 2; }
+int wkv6_b200_abi_version(void) { return 3; }
 /* Debug: enable != 0 allocates a device buffer that CTA 0 of the chunk kernels fills with clock64() stamps (forward:
  * slots 0..31, backward: 64..95) and, from slot 128 on, every CTA < 1024 of the forward chunk kernel with
  * {globaltimer at start, SM id, globaltimer at end, 0}; `out` (host, 128 entries) receives the first 128 slots;
@@ -309,24 +342,6 @@ int wkv6_b200_debug_trace(int enable, unsigned long long* out) {
     }
     if (out && g_dbg) cudaMemcpy(out, g_dbg, 128 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     if (!enable && g_dbg) { cudaFree(g_dbg); g_dbg = nullptr; }
-    return 0;
-}
-/* Lend (or, with NULL / 0, take back) a device scratch buffer for the time-segmented forward of long sequences.  The
- * library never allocates or frees it; it is used by forward calls on whatever stream they run (one stream at a time). */
-int wkv6_b200_set_scratch(void* device_ptr, size_t bytes) {
-    if (device_ptr && !aligned16(device_ptr)) return fail(WKV6_E_BADARG, "set_scratch: misaligned pointer");
-    int dev = -1;
-    if (device_ptr) {
-        cudaPointerAttributes at;
-        if (cudaPointerGetAttributes(&at, device_ptr) != cudaSuccess || at.type != cudaMemoryTypeDevice) {
-            cudaGetLastError();
-            return fail(WKV6_E_BADARG, "set_scratch: not a device pointer");
-        }
-        dev = at.device;
-    }
-    g_scratch = device_ptr;
-    g_scratch_bytes = device_ptr ? bytes : 0;
-    g_scratch_device = dev;
     return 0;
 }
 int wkv6_b200_debug_trace_ctas(unsigned long long* out) {
@@ -342,11 +357,20 @@ long long wkv6_b200_launch_count(void) { return g_launches.load(); }
 void wkv6_b200_set_algo(int algo) { g_algo.store(algo); }
 int wkv6_b200_get_algo(void) { return g_algo.load(); }
 
+size_t wkv6_b200_forward_scratch_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
+    if (check_common(dtype, B, T, C, H) || B == 0 || T == 0 || ndirections <= 0) return 0;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.C = C; p.H = H; p.ndir = ndirections;
+    return segment_scratch_bytes(p, use_chunk(dtype, T) ? 2 : 4);
+}
+
 int wkv6_b200_forward(int dtype, int B, int T, int C, int H, const void* r, const void* k, const void* v, const void* w,
-                      const void* u, const float* s0, void* y, float* sT, void* ckpt, int reverse, void* stream) {
+                      const void* u, const float* s0, void* y, float* sT, void* ckpt, int reverse, void* scratch,
+                      size_t scratch_bytes, void* stream) {
     const FwdSet s = {r, k, v, w, u, s0, y, sT, ckpt};
     const int rv = reverse != 0;
-    return run_forward(dtype, B, T, C, H, &s, &rv, 1, stream);
+    return run_forward(dtype, B, T, C, H, &s, &rv, 1, scratch, scratch_bytes, stream);
 }
 
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
@@ -373,13 +397,14 @@ int wkv6_b200_bi_forward(int dtype, int B, int T, int C, int H,
                          const void* r_f, const void* k_f, const void* v_f, const void* w_f, const void* u_f,
                          const float* s0_f, void* y_f, float* sT_f, void* ckpt_f,
                          const void* r_b, const void* k_b, const void* v_b, const void* w_b, const void* u_b,
-                         const float* s0_b, void* y_b, float* sT_b, void* ckpt_b, int flags, void* stream) {
+                         const float* s0_b, void* y_b, float* sT_b, void* ckpt_b, int flags, void* scratch,
+                         size_t scratch_bytes, void* stream) {
     FwdSet sets[2];
     int rv[2];
     int n = 0;
     if (flags & WKV6_BI_L2R) { sets[n] = {r_f, k_f, v_f, w_f, u_f, s0_f, y_f, sT_f, ckpt_f}; rv[n++] = 0; }
     if (flags & WKV6_BI_R2L) { sets[n] = {r_b, k_b, v_b, w_b, u_b, s0_b, y_b, sT_b, ckpt_b}; rv[n++] = 1; }
-    return run_forward(dtype, B, T, C, H, sets, rv, n, stream);
+    return run_forward(dtype, B, T, C, H, sets, rv, n, scratch, scratch_bytes, stream);
 }
 
 int wkv6_b200_bi_backward(int dtype, int B, int T, int C, int H,

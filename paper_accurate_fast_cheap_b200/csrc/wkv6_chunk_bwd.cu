@@ -793,7 +793,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 
 int launch_bwd_chunk(const Params& p, cudaStream_t st) {
     const size_t smem = sizeof(BwdChunkSmem) + 1024;
-    cudaError_t e = cudaFuncSetAttribute(wkv6_bwd_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = opt_in_smem_once(wkv6_bwd_chunk_kernel, smem, 1);
     if (e != cudaSuccess) return (int)e;
     Params q = p;
     q.dbg = debug_trace_buffer();

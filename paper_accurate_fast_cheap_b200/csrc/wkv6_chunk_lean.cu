@@ -1,12 +1,30 @@
-// wkv6_chunk_lean.cu -- chunked WKV6 forward (bf16 I/O) on tcgen05 / TMEM / TMA, second version (default).
+// wkv6_chunk_lean.cu -- chunked (dense-contraction) WKV6 forward for bf16 I/O on tcgen05 / TMEM / TMA (sm_100a).
 //
-// Same function, tiles and MMA groups as wkv6_chunk.cu (reference: wenet/rwkv_v6/cuda/wkv6_cuda.cu:9-63; chunked form
-// SURVEY.md App. A.5) -- read the header of that file for the algebra.  What changed, and why (the first version was
-// ISSUE-bound: ~1150 instructions per thread and chunk, 52 % issue utilisation, 4 CTA-wide barriers per chunk):
+// Same function as the reference's kernel_forward (wenet/rwkv_v6/cuda/wkv6_cuda.cu:9-63; with an initial state:
+// wkv6state_cuda.cu:7-65), restated per chunk of L = 64 steps so that the O(L*N*N) work runs on
+// the 5th-gen tensor cores:
+//     l_t = -exp(w_t) (log2 units, clamped at -5*log2e), A_t = exclusive cumsum, A+_t = inclusive cumsum
+//     P[p][q]  = sum_j r_p[j] k_q[j] 2^(A_p[j] - A+_q[j])   (q before p),  P[p][p] = sum_j r_p u k_p
+//     Y        = P V  +  (r_p 2^A_p) S^T                     S' = S diag(2^A_L) + V^T (k_q 2^(A_L - A+_q))
+// Overflow-free factorisation: the chunk is cut into four 16-step sub-blocks; every factor is taken relative to
+// the START of the row's sub-block I:  Rtil_p = r_p 2^(A_p - a_I) (<= |r|),  Ktil(I)_q = k_q 2^(a_I - A+_q)
+// (<= |k| for earlier sub-blocks, <= 2^(16*7.2) inside the diagonal sub-block: finite in bf16/fp32).
+//
+// One CTA (256 threads) per (direction, batch, head) [x time segment]; two CTAs per SM overlap each other's latency.
+//   G1 (x4): P^T[:, block I] = Ktil(I) [64 q x 64 j, K-major A]  x  Rtil[block I] [16 p x 64 j, K-major B]   M64 N16 K64
+//   G3     : Y   = Rst [64 p x 64 j, K-major A] x S' [64 j x 64 i, MN-major B]                              M64 N64 K64
+//   G2     : Y  += P^T tile [64 q x 64 p, MN-major A] x V [64 q x 64 i, MN-major B, straight from TMA]
+//   G4     : dS^T[j][i] = Ktil(4) [64 q x 64 j, MN-major A] x V [MN-major B]
+// All tiles are [64][64] bf16 with 128-byte rows and the 128B swizzle, so the same bytes serve as K-major or
+// MN-major operands (conventions verified on hardware by tests/probes/umma_probe.cu).  Accumulators live in TMEM
+// (P^T, Y, dS^T: 3 x 64 columns) and are read with tcgen05.ld.16x256b; the fp32 state S^T[j][i] stays in
+// registers in that fragment layout for the whole sequence.  The Ktil variants are stored compactly (variant I holds
+// the rows of sub-blocks <= I only: 28 KB instead of 40 KB, bases in ktbase()).
+//
+// How the kernel got here from a straightforward first version (~1150 instructions per thread and chunk, 52 % issue
+// utilisation, 4 CTA-wide barriers per chunk; history in DESIGN.md):
 //   * operand tiles are produced with packed bf16x2 arithmetic (HMUL2.BF16 on the raw TMA bits; the decay factors are
 //     computed in fp32, rounded once to bf16x2): no bf16->fp32 unpacking of r/k, half the multiplies, no F2FP per tile;
-//   * time direction is a template parameter: every row index, Ktil variant base and causal-mask predicate is a
-//     compile-time function of the thread coordinates;
 //   * the causal mask is resolved per 16x16 block (warp-uniform: keep / zero / diagonal), only diagonal blocks pay
 //     per-element selects;
 //   * TMEM fragments go to the swizzled operand tiles with stmatrix.x4 (2 per 16x32 fragment instead of 8 STS.32);
@@ -15,8 +33,6 @@
 //     is exposed; 3 CTA-wide barriers per chunk.
 // Log-decays are kept with the opposite sign here (m = -l >= 0) so that the clamp is one FMNMX.
 #include "wkv6_fwd_tiles.cuh"
-#include <cstdio>
-#include <cstdlib>
 
 namespace wkv6 {
 
@@ -496,22 +512,18 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
         p.dbg[129 + 4 * blockIdx.x] = smid;
     }
     const int ntot = (p.T + CL - 1) / CL;
-    if (p.nseg <= 1) {
-        lean_body(p, sm, D, b, h, bh, D.reverse != 0, 0, ntot, D.s0 ? D.s0 + (size_t)bh * N * N : nullptr,
-                  D.sT ? D.sT + (size_t)bh * N * N : nullptr, nullptr, p.skip_y != 0, D.ckpt != nullptr);
-    } else {
-        // time-segmented: pass 1 leaves every segment's local state (from S = 0) and decay product in the scratch, a small
-        // scan kernel turns them into the segment-start states, pass 2 recomputes every segment from its start state
-        const int cbeg = seg * p.seg_chunks;
-        const int nloc = min(p.seg_chunks, ntot - cbeg);
-        float* slot = p.seg_state + ((size_t)seq * nseg + seg) * N * N;
-        if (p.seg_mode == 1)
-            lean_body(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, nullptr, slot, p.seg_decay + ((size_t)seq * nseg + seg) * N,
-                      true, false);
-        else
-            lean_body(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, slot,
-                      (seg == nseg - 1 && D.sT) ? D.sT + (size_t)bh * N * N : nullptr, nullptr, p.skip_y != 0, D.ckpt != nullptr);
-    }
+    // ONE call site of the body (three inlined copies were 9 500 SASS instructions, ~150 KB of instruction cache for two
+    // co-resident CTAs).  Unsegmented: the whole sequence from S_0 to S_T.  Time-segmented: pass 1 (seg_mode 1) leaves every
+    // segment's local state (from S = 0) and decay product in the scratch, a small scan kernel turns them into the
+    // segment-start states, pass 2 (seg_mode 2) recomputes every segment from its start state.
+    const bool segd = p.nseg > 1, pass1 = segd && p.seg_mode == 1;
+    const int cbeg = segd ? seg * p.seg_chunks : 0;
+    const int nloc = segd ? min(p.seg_chunks, ntot - cbeg) : ntot;
+    float* const slot = segd ? p.seg_state + ((size_t)seq * nseg + seg) * N * N : nullptr;
+    const float* const s0p = pass1 ? nullptr : segd ? slot : (D.s0 ? D.s0 + (size_t)bh * N * N : nullptr);
+    float* const sTp = pass1 ? slot : ((!segd || seg == nseg - 1) && D.sT) ? D.sT + (size_t)bh * N * N : nullptr;
+    float* const dec = pass1 ? p.seg_decay + ((size_t)seq * nseg + seg) * N : nullptr;
+    lean_body(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, s0p, sTp, dec, pass1 || p.skip_y != 0, !pass1 && D.ckpt != nullptr);
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -522,7 +534,7 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
 // Segment scan: S_start[0] = S_0 (or 0), S_start[s+1][i][j] = S_start[s][i][j] * D_s[j] + dS_s[i][j]; the slots that pass 1
 // filled with dS_s are overwritten with S_start[s].  One thread per state element, grid = sequences x 16: every thread
 // first loads its element of all segments (independent loads, all in flight), then runs the recurrence from registers.
-constexpr int kMaxSeg = 40;   // pick_segments: nseg <= 296 / 8 = 37
+constexpr int kMaxSeg = 40;   // pick_segments clamps to this (nseq >= 8 gives <= 37 anyway)
 __global__ void __launch_bounds__(256) wkv6_seg_scan_kernel(const __grid_constant__ Params p) {
     const int BH = p.B * p.H;
     const int seq = blockIdx.x >> 4, ds = seq / BH, bh = seq - ds * BH;
@@ -556,6 +568,7 @@ static int pick_segments(const Params& p, size_t scratch_bytes, int min_seg, int
     if (nseq <= 0 || nseq * min_seg > 296 || ntot < 32) return 0;
     int nseg = 296 / nseq;                       // 148 SMs x 2 resident CTAs
     if (nseg > ntot / 8) nseg = ntot / 8;
+    if (nseg > kMaxSeg) nseg = kMaxSeg;          // wkv6_seg_scan_kernel keeps one register pair per segment
     if (nseg < min_seg) return 0;
     int sc = (ntot + nseg - 1) / nseg;
     nseg = (ntot + sc - 1) / sc;                 // no empty segments
@@ -564,8 +577,6 @@ static int pick_segments(const Params& p, size_t scratch_bytes, int min_seg, int
     *seg_chunks = sc;
     return nseg;
 }
-
-int launch_fwd_chunk_lean(const Params& p, cudaStream_t st);
 
 // Fills the segmentation fields of q (number of segments, chunks per segment, scratch layout); false: run unsegmented.
 bool plan_segments(Params& q, void* scratch, size_t scratch_bytes, int min_seg) {
@@ -580,6 +591,13 @@ bool plan_segments(Params& q, void* scratch, size_t scratch_bytes, int min_seg) 
     return true;
 }
 
+// Scratch bytes with which a launch of this shape runs time-segmented (0: it runs one CTA per sequence whatever it is given).
+size_t segment_scratch_bytes(const Params& p, int min_seg) {
+    int sc = 0;
+    const int nseg = pick_segments(p, ~(size_t)0, min_seg, &sc);
+    return nseg ? (size_t)p.ndir * p.B * p.H * nseg * (N * N + N) * sizeof(float) : 0;
+}
+
 int launch_seg_scan(const Params& q, cudaStream_t st) {
     if (q.nseg > kMaxSeg) return (int)cudaErrorInvalidValue;
     wkv6_seg_scan_kernel<<<dim3(q.ndir * q.B * q.H * 16), dim3(256), 0, st>>>(q);
@@ -592,30 +610,20 @@ int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_by
     Params q = p;
     if (!plan_segments(q, scratch, scratch_bytes, 2)) return -1;
     q.seg_mode = 1;
-    int e = launch_fwd_chunk_lean(q, st);
+    int e = launch_fwd_chunk(q, st);
     if (e) return e;
     if ((e = launch_seg_scan(q, st))) return e;
     q.seg_mode = 2;
-    return launch_fwd_chunk_lean(q, st);
+    return launch_fwd_chunk(q, st);
 }
 
-int launch_fwd_chunk_lean(const Params& p, cudaStream_t st) {
+int launch_fwd_chunk(const Params& p, cudaStream_t st) {
     const size_t smem = sizeof(LeanSmem) + 1024;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(wkv6_fwd_chunk_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        cudaFuncSetAttribute(wkv6_fwd_chunk_lean_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        if (getenv("WKV6_DEBUG_OCC")) {
-            int nb = -1;
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, wkv6_fwd_chunk_lean_kernel, 256, smem);
-            fprintf(stderr, "[wkv6] fwd_chunk_lean: smem %zu B, resident CTAs/SM %d\n", smem, nb);
-        }
-        attr_set = true;
-    }
+    cudaError_t e = opt_in_smem_once(wkv6_fwd_chunk_lean_kernel, smem, 0);
+    if (e != cudaSuccess) return (int)e;
     Params q = p;
     q.dbg = debug_trace_buffer();
-    const cudaError_t e = launch_pdl(wkv6_fwd_chunk_lean_kernel, dim3(q.ndir * q.B * q.H * (q.nseg > 0 ? q.nseg : 1)), dim3(256), smem, st, q);
+    e = launch_pdl(wkv6_fwd_chunk_lean_kernel, dim3(q.ndir * q.B * q.H * (q.nseg > 0 ? q.nseg : 1)), dim3(256), smem, st, q);
     count_launch(1);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }

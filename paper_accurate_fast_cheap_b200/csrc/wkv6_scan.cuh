@@ -1,6 +1,6 @@
 // wkv6_scan.cuh -- parameter blocks shared by the kernels and the C ABI (wkv6_capi.cu).
 #pragma once
-#include <cstdlib>
+#include <atomic>
 #include "wkv6_common.cuh"
 
 namespace wkv6 {
@@ -40,17 +40,17 @@ struct Params {
     int seg_mode;                         // 1: pass 1 (local state + decay product of every segment), 2: pass 2 (outputs)
     float* seg_state;                     // [ndir][B*H][nseg][64 i][64 j]: pass 1 writes dS, the scan turns it into S_start
     float* seg_decay;                     // [ndir][B*H][nseg][64 j]: product of the per-step decays of the segment
-    int dir_interleave;                   // forward ws kernel: direction = blockIdx parity instead of blockIdx / (B*H)
     unsigned long long* dbg;              // optional clock64() trace of one CTA (wkv6_b200_debug_trace), else null
 };
 
-// launchers (wkv6_scan.cu / wkv6_chunk.cu); return cudaError_t as int
+// launchers (wkv6_scan.cu / wkv6_chunk_lean.cu / wkv6_chunk_bwd.cu); return cudaError_t as int
 int launch_fwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_bwd_scan(int dtype, const Params& p, cudaStream_t st);
 int launch_fwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05
 int launch_tmix_mix(int dtype, int B, int T, int C, const void* x, const void* x_edge, const void* m, const void* const* maa, int reverse,
                     void* const* out, cudaStream_t st);
 bool plan_segments(Params& q, void* scratch, size_t scratch_bytes, int min_seg);
+size_t segment_scratch_bytes(const Params& p, int min_seg);
 int launch_seg_scan(const Params& q, cudaStream_t st);
 int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
@@ -71,11 +71,9 @@ unsigned long long* debug_trace_buffer();
     } while (0)
 
 
-// Launch with the programmatic-stream-serialization attribute (see pdl_wait() in wkv6_common.cuh); WKV6_NO_PDL=1 turns
-// the attribute off (plain stream order) for A/B timing.
+// Launch with the programmatic-stream-serialization attribute (see pdl_wait() in wkv6_common.cuh).
 template <typename Kernel>
 inline cudaError_t launch_pdl(Kernel kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const Params& q) {
-    static const bool on = getenv("WKV6_NO_PDL") == nullptr;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;
@@ -85,8 +83,25 @@ inline cudaError_t launch_pdl(Kernel kernel, dim3 grid, dim3 block, size_t smem,
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = on ? 1 : 0;
+    cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, q);
+}
+
+// The dynamic-shared-memory opt-in is a per-DEVICE function attribute: one bit per (kernel slot, device), so that a
+// process driving several GPUs opts in on each of them (and pays the driver call once per device, not per launch).
+template <typename Kernel>
+inline cudaError_t opt_in_smem_once(Kernel kernel, size_t bytes, int slot) {
+    static std::atomic<unsigned long long> done[4];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (done[slot].load(std::memory_order_acquire) & bit) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return e;
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    done[slot].fetch_or(bit, std::memory_order_release);
+    return cudaSuccess;
 }
 
 }  // namespace wkv6

@@ -29,9 +29,12 @@ void fwd_impl(int dtype, at::ScalarType dt, int64_t B, int64_t T, int64_t C, int
     check_btc(w, "w", dt, B, T, C); check_btc(y, "y", dt, B, T, C);
     TORCH_CHECK(u.is_cuda() && u.scalar_type() == dt && u.is_contiguous() && u.numel() == C, "wkv6: bad u");
     const c10::cuda::CUDAGuard guard(r.device());
+    // few, long sequences run time-segmented on a scratch buffer from the caching allocator (stream-ordered)
+    const size_t sc_bytes = wkv6_b200_forward_scratch_bytes(dtype, (int)B, (int)T, (int)C, (int)H, 1);
+    at::Tensor sc = at::empty({(int64_t)sc_bytes}, r.options().dtype(at::kByte));
     check_rc(wkv6_b200_forward(dtype, (int)B, (int)T, (int)C, (int)H, r.data_ptr(), k.data_ptr(), v.data_ptr(),
                                w.data_ptr(), u.data_ptr(), nullptr, y.data_ptr(), nullptr, nullptr, 0,
-                               at::cuda::getCurrentCUDAStream().stream()));
+                               sc_bytes ? sc.data_ptr() : nullptr, sc_bytes, at::cuda::getCurrentCUDAStream().stream()));
 }
 
 void bwd_impl(int dtype, at::ScalarType dt, int64_t B, int64_t T, int64_t C, int64_t H, const at::Tensor& r,

@@ -46,31 +46,26 @@ def _check_inputs(r, k, v, w, u, extra=()):
     return B, T, C, H
 
 
-_SCRATCH = {}
-SCRATCH_BYTES = 6 << 20      # covers every segmented launch (<= 296 segment slots x (64*64 + 64) floats)
-
-
-def _lend_scratch(t: torch.Tensor) -> None:
-    """Long sequences with few (batch, head) pairs run time-segmented (include/wkv6_b200.h: wkv6_b200_set_scratch); the
-    library never allocates, so the host side lends it a small per-device buffer once (torch caching allocator)."""
-    if t.size(1) < 2048:
-        return
-    key = t.device.index
-    if key not in _SCRATCH:
-        _SCRATCH[key] = torch.empty(SCRATCH_BYTES, device=t.device, dtype=torch.uint8)
-    buf = _SCRATCH[key]
-    _lib.check(_lib.lib().wkv6_b200_set_scratch(buf.data_ptr(), buf.numel()))
+_segmentation = True
 
 
 def set_segmentation(enabled: bool) -> None:
-    """Test / A-B switch: take the scratch buffer back so that every forward runs one CTA per sequence."""
-    global _lend_scratch_enabled
-    _lend_scratch_enabled = bool(enabled)
-    if not enabled:
-        _lib.check(_lib.lib().wkv6_b200_set_scratch(None, 0))
+    """Test / A-B switch: with False no scratch is handed to the forward, so every launch runs one CTA per sequence."""
+    global _segmentation
+    _segmentation = bool(enabled)
 
 
-_lend_scratch_enabled = True
+def _scratch(t: torch.Tensor, ndir: int):
+    """Scratch for the time-segmented forward of few, long sequences (include/wkv6_b200.h): allocated per call from the
+    caching allocator -- stream-ordered, so concurrent forwards on different streams never share a buffer -- and only for
+    shapes the library would segment (wkv6_b200_forward_scratch_bytes returns 0 otherwise)."""
+    B, T, C = t.size()
+    if not _segmentation or T < 2048:
+        return None, 0
+    nb = _lib.lib().wkv6_b200_forward_scratch_bytes(_dtype_code(t), B, T, C, C // HEAD_SIZE, ndir)
+    if nb == 0:
+        return None, 0
+    return torch.empty(nb, device=t.device, dtype=torch.uint8), nb
 
 
 def _check_state(s, B, H, dev):
@@ -96,11 +91,11 @@ def wkv6_forward_raw(r, k, v, w, u, s0=None, reverse=False, want_state=False, ck
     _check_state(s0, B, H, r.device)
     y = torch.empty_like(r)
     sT = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_state else None
-    if _lend_scratch_enabled:
-        _lend_scratch(r)
     with torch.cuda.device(r.device):
+        scratch, nb = _scratch(r, 1)
         _lib.check(_lib.lib().wkv6_b200_forward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u),
-                                                _p(s0), _p(y), _p(sT), _p(ckpt), int(bool(reverse)), _stream(r)))
+                                                _p(s0), _p(y), _p(sT), _p(ckpt), int(bool(reverse)), _p(scratch), nb,
+                                                _stream(r)))
     return y, sT
 
 
@@ -143,13 +138,12 @@ def bi_forward_raw(f, b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None, s0_b=None, 
     ba = tuple(_p(t) for t in b) if run_b else none5
     ck_f = ckpt[0] if (ckpt is not None and run_f) else None
     ck_b = ckpt[1] if (ckpt is not None and run_b) else None
-    if _lend_scratch_enabled:
-        _lend_scratch(ref[0])
     with torch.cuda.device(dev):
+        scratch, nb = _scratch(ref[0], int(run_f) + int(run_b))
         _lib.check(_lib.lib().wkv6_b200_bi_forward(_dtype_code(ref[0]), B, T, C, H,
                                                    *fa, _p(s0_f), _p(y_f), _p(sT_f), _p(ck_f),
                                                    *ba, _p(s0_b), _p(y_b), _p(sT_b), _p(ck_b), int(flags),
-                                                   _stream(ref[0])))
+                                                   _p(scratch), nb, _stream(ref[0])))
     return y_f, y_b, sT_f, sT_b
 
 

@@ -25,23 +25,29 @@ def test_header_symbols_are_exported(built):
     L = built.lib()
     for s in declared:
         assert hasattr(L, s), s
-    assert L.wkv6_b200_abi_version() == 2
+    assert L.wkv6_b200_abi_version() == 3
 
 
 def test_argument_validation_without_gpu(built):
     L = built.lib()
     # C != H*64
-    rc = L.wkv6_b200_forward(0, 1, 4, 96, 1, None, None, None, None, None, None, None, None, None, 0, None)
+    rc = L.wkv6_b200_forward(0, 1, 4, 96, 1, None, None, None, None, None, None, None, None, None, 0, None, 0, None)
     assert rc == -2 and b"64" in L.wkv6_b200_last_error()
-    rc = L.wkv6_b200_forward(7, 1, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None)
+    rc = L.wkv6_b200_forward(7, 1, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None, 0, None)
     assert rc == -3
     # empty batch is a no-op; NULL tensors with work to do are rejected before any launch
-    assert L.wkv6_b200_forward(0, 0, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None) == 0
-    assert L.wkv6_b200_forward(0, 1, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None) == -1
+    assert L.wkv6_b200_forward(0, 0, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None, 0, None) == 0
+    assert L.wkv6_b200_forward(0, 1, 4, 64, 1, None, None, None, None, None, None, None, None, None, 0, None, 0, None) == -1
     assert L.wkv6_b200_backward_workspace_bytes(1, 2, 10, 128, 2, 2) == 2 * 2 * 2 * 64 * 4
     assert L.wkv6_b200_backward_workspace_bytes(0, 2, 10, 128, 2, 2) == max(2 * 2 * 2 * 64 * 4 + 2 * 2 * 10 * 128 * 2,
                                                                             2 * L.wkv6_b200_checkpoint_bytes(2, 10, 128, 2))
     assert L.wkv6_b200_checkpoint_bytes(2, 130, 128, 2) == 2 * 2 * 3 * 64 * 64 * 2
+    # time segmentation: only few, long sequences; the size is what the planner will use (<= 40 segments per sequence)
+    assert L.wkv6_b200_forward_scratch_bytes(0, 16, 750, 512, 8, 2) == 0            # short
+    assert L.wkv6_b200_forward_scratch_bytes(0, 16, 30000, 512, 8, 2) == 0          # 256 sequences: SMs are full
+    assert L.wkv6_b200_forward_scratch_bytes(0, 1, 30000, 512, 8, 2) == 16 * 18 * (64 * 64 + 64) * 4
+    assert L.wkv6_b200_forward_scratch_bytes(0, 1, 40000, 256, 4, 1) == 4 * 40 * (64 * 64 + 64) * 4
+    assert L.wkv6_b200_forward_scratch_bytes(1, 1, 90000, 1024, 16, 2) > 0
 
 
 def test_torch_shim_registers_reference_schemas(built):
@@ -56,6 +62,45 @@ def test_torch_shim_registers_reference_schemas(built):
     def f(r: torch.Tensor, u: torch.Tensor, y: torch.Tensor):
         torch.ops.wkv6.forward_fp32(1, 1, 64, 1, r, r, r, r, u, y)
     assert "wkv6::forward_fp32" in str(f.graph)
+
+
+def _header_params(name):
+    hdr = open(os.path.join(ROOT, "include", "wkv6_b200.h")).read()
+    m = re.search(r"\b" + name + r"\s*\(([^;]*?)\)\s*;", hdr, re.S)
+    assert m, name
+    return [a.strip() for a in m.group(1).replace("\n", " ").split(",")]
+
+
+def test_integration_snippets_match_header(built, tmp_path):
+    """INTEGRATION.md level 0: the C++ stub compiles against include/wkv6_b200.h (and the torch headers), and the ctypes
+    stub declares exactly the header's parameter list (the round-1 snippets had drifted by one pointer)."""
+    import subprocess
+    from torch.utils import cpp_extension as ce
+    md = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    cpp = re.search(r"```cpp\n(.*?)```", md, re.S).group(1)
+    src = tmp_path / "snippet.cpp"
+    src.write_text(cpp)
+    inc = []
+    for p_ in ce.include_paths():
+        inc += ["-isystem", p_]
+    abi = int(getattr(torch._C, "_GLIBCXX_USE_CXX11_ABI", True))
+    subprocess.run(["g++", "-std=c++17", "-fsyntax-only", f"-D_GLIBCXX_USE_CXX11_ABI={abi}", "-I/usr/local/cuda/include",
+                    "-I" + os.path.join(ROOT, "include"), *inc, str(src)], check=True)
+    py = re.search(r"```python\n(import ctypes, torch.*?)```", md, re.S).group(1)
+    py = py.replace('ctypes.CDLL("libwkv6_b200.so")', f'ctypes.CDLL({built.LIB_PATH!r})')
+    ns = {}
+    exec(compile(py, "INTEGRATION.md", "exec"), ns)
+    params = _header_params("wkv6_b200_forward")
+    argtypes = ns["_L"].wkv6_b200_forward.argtypes
+    assert len(argtypes) == len(params) == 18
+    for a, t in zip(params, argtypes):
+        want = ctypes.c_int if a.startswith("int ") else ctypes.c_size_t if a.startswith("size_t ") else ctypes.c_void_p
+        assert t is want, (a, t)
+    # the package's own binding agrees with the header as well, for every compute entry point
+    L = built.lib()
+    for name in ("wkv6_b200_forward", "wkv6_b200_backward", "wkv6_b200_bi_forward", "wkv6_b200_bi_backward",
+                 "wkv6_b200_combine", "wkv6_b200_tmix_mix"):
+        assert len(getattr(L, name).argtypes) == len(_header_params(name)), name
 
 
 def test_no_cpu_fallback(built):

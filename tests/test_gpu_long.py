@@ -101,7 +101,7 @@ def test_cfg4_training_shape_bf16_gradients():
 @pytest.mark.parametrize("with_state", [False, True])
 def test_cfg3_time_segmented_forward(with_state):
     """configs[2] at 8 GPUs: ONE utterance per GPU (B = 1, 8 heads, both directions = 16 sequences of T = 30 000).  With
-    the scratch buffer lent (ops._lend_scratch) the forward runs time-segmented (pass 1 / segment scan / pass 2: three
+    a scratch buffer (ops._scratch, per call) the forward runs time-segmented (pass 1 / segment scan / pass 2: three
     launches); y, S_T and the chunk checkpoints agree with the one-CTA-per-sequence run and with the fp64 oracle."""
     pk = _pk()
     from paper_accurate_fast_cheap_b200 import ops
@@ -224,11 +224,80 @@ def test_time_segmented_two_segments_many_sequences():
     assert oracle.rel_err(s_f, sa) <= tol and oracle.rel_err(s_b, sb) <= tol
 
 
-def test_set_scratch_rejects_host_memory():
-    """The scratch must be device memory (the library records which device it lives on and segments only launches on
-    that device)."""
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_time_segmented_few_heads_long_T(dtype):
+    """B = 1, 4 heads, ONE direction, T = 40 000 (the configs[0] model size on a long recording): 4 sequences would ask for
+    70 segments; the planner clamps to the 40 the segment-scan kernel handles (this shape used to fail with
+    'invalid argument' after pass 1 had been launched).  Three launches, parity with the fp64 oracle."""
+    pk = _pk()
     from paper_accurate_fast_cheap_b200 import _lib
-    host = torch.empty(1 << 20, dtype=torch.uint8)
-    with pytest.raises(_lib.Wkv6Error):
-        _lib.check(_lib.lib().wkv6_b200_set_scratch(host.data_ptr(), host.numel()))
-    _lib.check(_lib.lib().wkv6_b200_set_scratch(None, 0))
+    B, T, H = 1, 40000, 4
+    inp = _inputs(B, T, H, dtype, seed=81)
+    g = _cuda(inp)
+    nb = _lib.lib().wkv6_b200_forward_scratch_bytes(0 if dtype == torch.bfloat16 else 1, B, T, H * 64, H, 1)
+    assert 0 < nb <= 4 * 40 * (64 * 64 + 64) * 4
+    n0 = pk.launch_count()
+    y, sT = pk.wkv6_forward_raw(g["r"], g["k"], g["v"], g["w"], g["u"], want_state=True)
+    torch.cuda.synchronize()
+    assert pk.launch_count() - n0 == 3
+    y_ref, s_ref = oracle.fwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], want_state=True, prec="f64")
+    assert oracle.rel_err(y, y_ref) <= TOL[dtype] and oracle.rel_err(sT, s_ref) <= TOL[dtype]
+
+
+def test_scratch_is_per_call_two_streams():
+    """ABI v3: the segmentation scratch is an argument of the call, not library state.  Two segmented forwards on two
+    streams at the same time (the reference's forward_parallel pattern, rwkv_wrapper_bidirectional.py:66-116) use two
+    buffers and both match the serial results; a too-small or NULL scratch runs unsegmented (1 launch), never fails."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import _lib
+    L = _lib.lib()
+    B, T, H = 1, 20011, 4
+    a, b = _cuda(_inputs(B, T, H, torch.bfloat16, seed=91)), _cuda(_inputs(B, T, H, torch.bfloat16, seed=92, layer=4))
+    ya, _ = pk.wkv6_forward_raw(a["r"], a["k"], a["v"], a["w"], a["u"])
+    yb, _ = pk.wkv6_forward_raw(b["r"], b["k"], b["v"], b["w"], b["u"], reverse=True)
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    outs = []
+    for _ in range(4):                      # several rounds so that the two triples really interleave
+        with torch.cuda.stream(s1):
+            y1, _ = pk.wkv6_forward_raw(a["r"], a["k"], a["v"], a["w"], a["u"])
+        with torch.cuda.stream(s2):
+            y2, _ = pk.wkv6_forward_raw(b["r"], b["k"], b["v"], b["w"], b["u"], reverse=True)
+        outs.append((y1, y2))
+    torch.cuda.synchronize()
+    for y1, y2 in outs:
+        assert torch.equal(y1, ya) and torch.equal(y2, yb)
+    # NULL / undersized scratch: one launch, same tolerance class
+    p = lambda t: t.data_ptr()
+    y = torch.empty_like(a["r"])
+    small = torch.empty(1024, device="cuda", dtype=torch.uint8)
+    for sc, nb in ((None, 0), (small.data_ptr(), small.numel())):
+        n0 = pk.launch_count()
+        _lib.check(L.wkv6_b200_forward(0, B, T, H * 64, H, p(a["r"]), p(a["k"]), p(a["v"]), p(a["w"]), p(a["u"]), None, p(y),
+                                       None, None, 0, sc, nb, torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        assert pk.launch_count() - n0 == 1
+        assert oracle.rel_err(y.cpu(), ya.cpu().double()) <= 1e-2
+    # misaligned scratch is rejected before any launch
+    big = torch.empty((8 << 20) + 16, device="cuda", dtype=torch.uint8)
+    rc = L.wkv6_b200_forward(0, B, T, H * 64, H, p(a["r"]), p(a["k"]), p(a["v"]), p(a["w"]), p(a["u"]), None, p(y), None, None, 0,
+                             big.data_ptr() + 4, 8 << 20, torch.cuda.current_stream().cuda_stream)
+    assert rc == -1
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_devices_one_process():
+    """the dynamic-shared-memory opt-in is a per-device function attribute; one process driving cuda:0 and then
+    cuda:1 must get it on both (bf16 forward + backward on each device against the oracle)."""
+    pk = _pk()
+    inp = _inputs(2, 200, 4, torch.bfloat16, seed=95)
+    y_ref, _ = oracle.fwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], prec="f64")
+    ref = oracle.bwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], inp["gy"], prec="f64")
+    for d in (0, 1):
+        g = {n: t.to(f"cuda:{d}") for n, t in inp.items() if isinstance(t, torch.Tensor)}
+        y, _ = pk.wkv6_forward_raw(g["r"], g["k"], g["v"], g["w"], g["u"])
+        o = pk.wkv6_backward_raw(g["r"], g["k"], g["v"], g["w"], g["u"], g["gy"])
+        torch.cuda.synchronize(d)
+        assert oracle.rel_err(y, y_ref) <= TOL[torch.bfloat16]
+        for x, r_ in zip(o[:5], ref[:5]):
+            assert oracle.rel_err(x, r_) <= TOL[torch.bfloat16]
