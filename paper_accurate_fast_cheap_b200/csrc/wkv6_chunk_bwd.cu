@@ -272,6 +272,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         int rows[4];
         {
             float rr[4][4], kk[4][4], l2[4][4], bsum[4];
+            float xmax = 0.f;
 #pragma unroll
             for (int r = 0; r < 4; r++) {
                 const int pos = 16 * I + 4 * rg + r;
@@ -291,10 +292,23 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     bs = fmaf(rr[r][e] * u4[e], kk[r][e], bs);
                     const float x = ex2(w4[e] * kLog2e);            // exp(w)
                     ew[r][e] = x;
+                    xmax = fmaxf(xmax, x);
                     const float l = fmaxf(-x * kLog2e, -kClampL2);
                     l2[r][e] = valid ? l : 0.f;
                 }
                 bsum[r] = bs;
+            }
+            // d l / d w where the decay floor is active (exp(w) > 5; never with trained decays, so the whole warp skips it):
+            // the recurrence ran with 2^l instead of 2^lt, so the H_p computed below is (floored decay) x dL/d(decay); the
+            // true step has (true decay) x the same derivative to first order: rescale exp(w) by 2^(lt - l)
+            if (__any_sync(0xffffffffu, xmax * kLog2e > kClampL2)) {
+#pragma unroll
+                for (int r = 0; r < 4; r++)
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const float x = fminf(ew[r][e], 1e30f);
+                        ew[r][e] = x * ex2(fminf(kClampL2 - x * kLog2e, 0.f));
+                    }
             }
 #pragma unroll
             for (int e = 0; e < 4; e++) {

@@ -58,9 +58,16 @@ struct LeanSmem {
 // The CTA processes the chunks [cbeg, cbeg + nchunks) of its sequence (processing order), starting from the state *s0p
 // (null: zero) and leaving the final state in *sTp (unless null); decay_out (unless null) receives the product of all
 // per-step decays of that range per key channel.  Unsegmented: cbeg = 0, nchunks = all.
+// kStateOnly: pass 1 of the time-segmented forward (no outputs, no checkpoints, S_0 = 0, decay product out) -- a
+// compile-time mode, so that the normal instantiation carries none of its code (and vice versa).
+template <bool kStateOnly>
 __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
-                                          const bool REV, const int cbeg, const int nchunks, const float* s0p, float* sTp,
-                                          float* decay_out, const bool skip_y, const bool ckpt_on) {
+                                          const bool REV, const int cbeg, const int nchunks, const float* s0p_, float* sTp,
+                                          float* decay_out_, const bool skip_y_, const bool ckpt_on_) {
+    const float* const s0p = kStateOnly ? nullptr : s0p_;
+    float* const decay_out = kStateOnly ? decay_out_ : nullptr;
+    const bool skip_y = kStateOnly ? true : skip_y_;
+    const bool ckpt_on = kStateOnly ? false : ckpt_on_;
     const int tid = threadIdx.x, lane = tid & 31;
     const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     // warp index through a lane-0 broadcast: the compiler then keeps it (and everything derived from it: MMA operands,
@@ -512,8 +519,9 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
         p.dbg[129 + 4 * blockIdx.x] = smid;
     }
     const int ntot = (p.T + CL - 1) / CL;
-    // ONE call site of the body (three inlined copies were 9 500 SASS instructions, ~150 KB of instruction cache for two
-    // co-resident CTAs).  Unsegmented: the whole sequence from S_0 to S_T.  Time-segmented: pass 1 (seg_mode 1) leaves every
+    // Two instantiations of the body: the normal one and the state-only pass 1 (a single call site with run-time mode flags
+    // was measured 3 us per launch SLOWER on the bench: 43.6 vs 40.5 us -- the pass-1 code and flags sit in the chunk loop).
+    // Unsegmented: the whole sequence from S_0 to S_T.  Time-segmented: pass 1 (seg_mode 1) leaves every
     // segment's local state (from S = 0) and decay product in the scratch, a small scan kernel turns them into the
     // segment-start states, pass 2 (seg_mode 2) recomputes every segment from its start state.
     const bool segd = p.nseg > 1, pass1 = segd && p.seg_mode == 1;
@@ -523,7 +531,10 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
     const float* const s0p = pass1 ? nullptr : segd ? slot : (D.s0 ? D.s0 + (size_t)bh * N * N : nullptr);
     float* const sTp = pass1 ? slot : ((!segd || seg == nseg - 1) && D.sT) ? D.sT + (size_t)bh * N * N : nullptr;
     float* const dec = pass1 ? p.seg_decay + ((size_t)seq * nseg + seg) * N : nullptr;
-    lean_body(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, s0p, sTp, dec, pass1 || p.skip_y != 0, !pass1 && D.ckpt != nullptr);
+    if (pass1)
+        lean_body<true>(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, nullptr, sTp, dec, true, false);
+    else
+        lean_body<false>(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, s0p, sTp, nullptr, p.skip_y != 0, D.ckpt != nullptr);
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

@@ -24,7 +24,7 @@ def wkv6_recurrence(r, k, v, w, u, s0=None, rev=False):
 def make_inputs(B, T, H, N, seed=777, dtype=torch.float64, layer=0, n_layers=12, w_mode="init",
                 with_state=False):
     """Synthetic op-level inputs of SURVEY.md section 8(d): r,k,v ~ N(0,1); w = time_decay init + 0.5 N(0,1)
-    (model.py:248-251) or the stress variant U(-8, 1.5); u = time_faaaa init (model.py:256-260)."""
+    (model.py:248-251), the stress variant U(-8, 1.5) or the clamp variant (a third of the channels in U(1.7, 3.0)); u = time_faaaa init (model.py:256-260)."""
     C = H * N
     g = torch.Generator().manual_seed(seed)
     r, k, v, gy = (torch.randn(B, T, C, generator=g, dtype=torch.float64) for _ in range(4))
@@ -35,6 +35,13 @@ def make_inputs(B, T, H, N, seed=777, dtype=torch.float64, layer=0, n_layers=12,
         w = base.view(1, 1, C) + 0.5 * torch.randn(B, T, C, generator=g, dtype=torch.float64)
     elif w_mode == "stress":
         w = torch.rand(B, T, C, generator=g, dtype=torch.float64) * 9.5 - 8.0
+    elif w_mode == "clamp":
+        # the region where the chunk kernels' per-step decay floor is active (w > ln 5 = 1.609, csrc/wkv6_umma.cuh):
+        # every third channel decays with w ~ U(1.7, 3.0), i.e. exp(-exp(w)) between 4e-3 and 2e-9; the rest: init
+        base = -6 + 5 * (n / max(C - 1, 1)) ** (0.7 + 1.3 * ratio)
+        w = base.view(1, 1, C) + 0.5 * torch.randn(B, T, C, generator=g, dtype=torch.float64)
+        hot = 1.7 + 1.3 * torch.rand(B, T, C, generator=g, dtype=torch.float64)
+        w = torch.where((torch.arange(C) % 3 == 1).view(1, 1, C), hot, w)
     else:
         raise ValueError(w_mode)
     zig = ((n + 1) % 3 - 1) * 0.1

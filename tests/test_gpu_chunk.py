@@ -24,7 +24,8 @@ def chunk_algo():
     (2, 250, 4, False, "init"),      # BASELINE config 1 shape (bf16)
     (1, 1, 1, False, "init"),
     (2, 130, 2, True, "init"),       # ragged tail + initial state
-    (3, 53, 2, True, "stress"),      # strong decays: exercises the sub-block factorisation and the clamp
+    (3, 53, 2, True, "stress"),      # strong decays (exp(w) <= 4.48: the sub-block factorisation; the decay floor never fires)
+    (2, 200, 2, True, "clamp"),      # a third of the channels beyond the decay floor (exp(w) in 5.5 .. 20)
     (2, 750, 8, False, "init"),      # BASELINE config 2 sequence length
 ])
 def test_chunk_forward_matches_oracle(chunk_algo, rev, B, T, H, with_state, w_mode):
@@ -59,6 +60,7 @@ def test_chunk_bidirectional_one_launch(chunk_algo):
     (1, 64, 1, False, "init"),
     (2, 130, 2, True, "init"),       # ragged tail, initial state, gradient into the final state
     (3, 53, 2, True, "stress"),
+    (2, 200, 2, True, "clamp"),      # decay floor active on a third of the channels (chunk kernels only clamp)
     (2, 750, 8, False, "init"),      # BASELINE config 2 sequence length
 ])
 def test_bf16_backward_both_kernels(algo, rev, B, T, H, with_state, w_mode):
@@ -113,3 +115,71 @@ def test_chunk_backward_uses_forward_checkpoints():
     ((yf.float() * ga["gy"].float()).sum() + (yb.float() * gb["gy"].float()).sum()).backward()
     assert pk.launch_count() - n0 == 2
     assert oracle.rel_err(lf[3].grad, ra[3]) <= 2e-2 and oracle.rel_err(lb[3].grad, rb[3]) <= 2e-2
+
+
+@pytest.mark.parametrize("rev", [False, True])
+def test_decay_floor_region_errors_are_reported(rev, capsys):
+    """The only semantic approximation of the bf16 chunk path -- per-step decays below exp(-5) are treated as exp(-5) in
+    the state recurrence, and gw of such a step is scaled by true / floored decay -- measured where it is active
+    (w ~ U(1.7, 3.0) on a third of the channels), forward and backward, against the fp64 oracle.  DESIGN.md section 4.1
+    quotes the numbers this test prints."""
+    import paper_accurate_fast_cheap_b200 as pk
+    inp = _inputs(2, 300, 4, torch.bfloat16, "clamp", True)
+    g = _cuda(inp)
+    ck = pk.ops.checkpoint_buffer(g["r"], 1)
+    y, sT = pk.wkv6_forward_raw(g["r"], g["k"], g["v"], g["w"], g["u"], s0=g["s0"], reverse=rev, want_state=True, ckpt=ck[0])
+    out = pk.wkv6_backward_raw(g["r"], g["k"], g["v"], g["w"], g["u"], g["gy"], s0=g["s0"], gsT=g["gsT"], reverse=rev,
+                               want_gs0=True, ckpt=ck[0])
+    y_ref, sT_ref = oracle.fwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], inp["s0"], rev=rev, want_state=True, prec="f64")
+    ref = oracle.bwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], inp["gy"], s0=inp["s0"], gsT=inp["gsT"], rev=rev, prec="f64")
+    errs = {"y": oracle.rel_err(y, y_ref), "sT": oracle.rel_err(sT, sT_ref)}
+    for name, a, b in zip(("gr", "gk", "gv", "gw", "gu", "gs0"), out, ref):
+        errs[name] = oracle.rel_err(a, b)
+    # gw restricted to the channels beyond the floor, on its own scale
+    hot = (torch.arange(inp["w"].shape[-1]) % 3 == 1)
+    errs["gw_hot_channels_vs_max_gw"] = float((out[3].cpu().double() - ref[3])[..., hot].abs().max() / ref[3].abs().max())
+    with capsys.disabled():
+        print("\ndecay-floor region (rev=%s): " % rev + ", ".join(f"{k} {v:.2e}" for k, v in errs.items()))
+    for k_, v_ in errs.items():
+        assert v_ <= 2e-2, (k_, v_)
+
+
+@pytest.mark.parametrize("use_ckpt", [True, False])
+@pytest.mark.parametrize("flags", [1, 2])
+def test_bi_backward_with_a_dropped_direction(flags, use_ckpt):
+    """Direction dropout is a TRAINING feature (rwkv_wrapper_bidirectional_direction_dropout_both.py:53-71): forward and
+    backward launches with only one flag bit set, checkpointed and recompute paths; the dropped set is neither read nor
+    written (its tensors are poisoned with NaN), the running set matches the oracle."""
+    import paper_accurate_fast_cheap_b200 as pk
+    from paper_accurate_fast_cheap_b200 import ops
+    a = _inputs(2, 300, 4, torch.bfloat16, seed=1)
+    b = _inputs(2, 300, 4, torch.bfloat16, seed=2, layer=7)
+    ga, gb = _cuda(a), _cuda(b)
+    run_f = bool(flags & 1)
+    dead = gb if run_f else ga
+    for n in "rkvw":
+        dead[n].fill_(float("nan"))
+    dead["gy"].fill_(float("nan"))
+    f, r_ = tuple(ga[n] for n in "rkvwu"), tuple(gb[n] for n in "rkvwu")
+    ck = ops.checkpoint_buffer(ga["r"], 2) if use_ckpt else None
+    n0 = pk.launch_count()
+    y_f, y_b, _, _ = pk.bi_forward_raw(f, r_, flags=flags, ckpt=ck)
+    of, ob = pk.bi_backward_raw(f, r_, ga["gy"] if run_f else None, None if run_f else gb["gy"], flags=flags, ckpt=ck)
+    assert pk.launch_count() - n0 == (2 if use_ckpt else 3)
+    assert (y_b is None and ob[0] is None) if run_f else (y_f is None and of[0] is None)
+    src, got_y, got = (a, y_f, of) if run_f else (b, y_b, ob)
+    y_ref, _ = oracle.fwd(src["r"], src["k"], src["v"], src["w"], src["u"], rev=not run_f, prec="f64")
+    ref = oracle.bwd(src["r"], src["k"], src["v"], src["w"], src["u"], src["gy"], rev=not run_f, prec="f64")
+    assert oracle.rel_err(got_y, y_ref) <= 2e-2
+    for name, x, y in zip(("gr", "gk", "gv", "gw", "gu"), got[:5], ref[:5]):
+        assert oracle.rel_err(x, y) <= 2e-2, name
+    # autograd: BiWKV6 with a dropped direction returns None for it and no gradient for its inputs
+    lf = [t.clone().requires_grad_(True) for t in f]
+    lb = [t.clone().requires_grad_(True) for t in r_]
+    yf, yb = pk.bi_wkv6(lf, lb, run_l2r=run_f, run_r2l=not run_f)
+    live, gy = (yf, ga["gy"]) if run_f else (yb, gb["gy"])
+    assert (yb if run_f else yf) is None
+    (live.float() * gy.float()).sum().backward()
+    run_set, drop_set = (lf, lb) if run_f else (lb, lf)
+    assert all(t.grad is None for t in drop_set)
+    assert oracle.rel_err(run_set[3].grad, ref[3]) <= 2e-2 and oracle.rel_err(run_set[0].grad, ref[0]) <= 2e-2
