@@ -11,8 +11,9 @@ Beside the headline the same JSON line carries (each is a leg of `--legs`, all o
   infer     the forward alone (inference; configs[1] literally)
   e2e       the headline step through the C ABI with HOST buffers: pinned slab -> H2D -> fwd -> bwd -> D2H, every step
   cfg4      configs[3]: B=8 per GPU, direction dropout (seeded CPU Bernoulli sequence of ..._direction_dropout_both.py)
-            as the launches' flags, and the NCCL gradient all-reduce of the 24 x 1 249 792 bf16 Tmix gradients, one
-            bucket per block, issued as the backward proceeds (DDP's find_unused_parameters=True volume)
+            as the launches' flags, and the NCCL gradient all-reduce of the 24 x 1 249 792 bf16 Tmix gradients in
+            DDP-sized buckets (4 blocks = 20 MB), each issued on a side stream as soon as the backward launch of its last
+            block is queued (DDP's find_unused_parameters=True volume: a dropped direction contributes zeros)
   cfg5      configs[4]: fp32, B=1, T=90 000, d_model 1024, 16 heads, one bidirectional block, forward
   longform  configs[2]: 8 utterances x T=30 000 in total, sharded over the ranks (strong scaling), forward
   ref_cuda  the reference's own CUDA kernels (oracle/_ref/libwkv6_ref.so = wkv6_cuda.cu unmodified) on the same GPU
@@ -414,12 +415,17 @@ def run_b200(args):
                 seq.append(_lib.BI_L2R if Bernoulli(0.8).sample((1,)) <= 0.5 else _lib.BI_R2L)
         torch.set_rng_state(cpu_state)
         NP = TMIX_PARAMS_PER_DIRECTION
+        PER_BUCKET = 4                                                    # blocks per bucket: 20 MB, DDP's bucket_cap_mb=25 scale
+        NBK = (NL + PER_BUCKET - 1) // PER_BUCKET
         gb = torch.Generator(device=dev).manual_seed(4242 + rank)
-        synth = [torch.randn(2 * NP, device=dev, generator=gb).mul_(1e-2).to(dt) for _ in range(NL)]   # GEMM / LoRA / LN grads
-        buckets = [torch.empty(2 * NP, device=dev, dtype=dt) for _ in range(NL)]
+        # the surrounding model's gradients (GEMM / LoRA / LayerNorm weights) are outside the path: synthetic, fixed
+        synth = [torch.randn(2 * NP, device=dev, generator=gb).mul_(1e-2).to(dt) for _ in range(NL)]
+        buckets = [torch.cat([synth[l] for l in range(k * PER_BUCKET, min(NL, (k + 1) * PER_BUCKET))]) for k in range(NBK)]
+        half_of = lambda l, d: buckets[l // PER_BUCKET][((l % PER_BUCKET) * 2 + d) * NP:((l % PER_BUCKET) * 2 + d + 1) * NP]
+        zeroed = [[False, False] for _ in range(NL)]
         U_OFF = 5 * C + 2 * 128 * C + C + 2 * 64 * C                     # time_faaaa inside one direction's flat gradient
         comm = torch.cuda.Stream()
-        evs = [torch.cuda.Event() for _ in range(NL)]
+        evs = [torch.cuda.Event() for _ in range(NBK)]
         cursor = [0]
 
         def step(collective):
@@ -437,22 +443,25 @@ def run_b200(args):
                 gb_ = [g[:B4] for g in gouts[l][1]]
                 bwd_call(B4, [x[:B4] if x.dim() == 3 else x for x in f], [x[:B4] if x.dim() == 3 else x for x in b],
                          ckpts[l][0], ckpts[l][1], gf, gb_, fl[l])
-                # the block's gradient bucket: the surrounding model's gradients (synthetic here: the GEMMs are outside the
-                # path) with this launch's gu.sum(0) (model.py:151) in time_faaaa's slot; a dropped direction's half is
-                # zero, which is what DDP(find_unused_parameters=True) reduces for parameters that got no gradient
-                bk_ = buckets[l]
-                bk_.copy_(synth[l])
+                # the block's slice of its gradient bucket: this launch's gu.sum(0) (model.py:151) goes into time_faaaa's
+                # slot; a dropped direction's half is zero, which is what DDP(find_unused_parameters=True) reduces for
+                # parameters that got no gradient (the all-reduce volume does not depend on the dropout outcome)
                 for d, (g5, bit) in enumerate(((gf[4], _lib.BI_L2R), (gb_[4], _lib.BI_R2L))):
-                    half = bk_[d * NP:(d + 1) * NP]
+                    half = half_of(l, d)
                     if fl[l] & bit:
+                        if zeroed[l][d]:
+                            half.copy_(synth[l][d * NP:(d + 1) * NP])
+                            zeroed[l][d] = False
                         torch.sum(g5, 0, out=half[U_OFF:U_OFF + C])
-                    else:
+                    elif not zeroed[l][d]:
                         half.zero_()
-                if collective and world > 1:
-                    evs[l].record()
+                        zeroed[l][d] = True
+                if collective and world > 1 and l % PER_BUCKET == 0:   # the bucket's last block (backward order) is done
+                    k_ = l // PER_BUCKET
+                    evs[k_].record()
                     with torch.cuda.stream(comm):
-                        comm.wait_event(evs[l])
-                        works.append(dist.all_reduce(bk_, op=dist.ReduceOp.AVG, async_op=True))
+                        comm.wait_event(evs[k_])
+                        works.append(dist.all_reduce(buckets[k_], op=dist.ReduceOp.AVG, async_op=True))
             for w_ in works:
                 w_.wait()
             if works:
@@ -466,7 +475,7 @@ def run_b200(args):
         ms_without, _ = run(False)
         res = {"metric": "encoder frames/s (bi-WKV6 fwd+bwd, direction dropout, gradient all-reduce)",
                "workload": f"configs[3]: {B4} utterances x T={T} per GPU x {world} GPUs, 12 blocks, bf16, direction dropout p=0.2 "
-                           "(dir_layer_drop_both), one bf16 gradient bucket of 2 x 1 249 792 per block",
+                           f"(dir_layer_drop_both), bf16 gradient buckets of {PER_BUCKET} blocks x 2 x 1 249 792",
                "value": world * B4 * T / (ms_with * 1e-3), "unit": "frames/s", "ms_per_step": ms_with,
                "ms_per_step_without_collective": ms_without, "steps": n4, "gpu_launches": n_l,
                "directions_run": {"both": seq[:n4 * NL].count(BOTH), "l2r_only": seq[:n4 * NL].count(_lib.BI_L2R),
@@ -490,8 +499,8 @@ def run_b200(args):
             dist.all_gather(allsig, sig)
             same = all(bool((s_ == allsig[0]).all()) for s_ in allsig)
             assert same, "gradient buckets differ across ranks after the all-reduce"
-            res.update({"collective": "NCCL all_reduce(AVG) bf16, one bucket per block on a side stream, issued right after the "
-                                      "block's backward launch", "allreduce_alone_ms": alone, "exposed_ms": exposed,
+            res.update({"collective": f"NCCL all_reduce(AVG) bf16, {NBK} buckets of {PER_BUCKET} blocks on a side stream, each issued "
+                                      "right after the backward launch of its last block", "allreduce_alone_ms": alone, "exposed_ms": exposed,
                         "overlap_fraction": max(0.0, min(1.0, 1.0 - exposed / max(alone, 1e-9))),
                         "buckets_identical_across_ranks": same})
         else:

@@ -92,7 +92,14 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     uint8_t* const o_gk = sm.qmt;   // chunk rewrites them only after thread 0 has waited for the TMA stores
     uint8_t* const o_gv = sm.pt;
 
-    pdl_launch_dependents();
+    if (p.dbg && tid == 0 && blockIdx.x < 1024) {   // debug trace only: per-CTA {start, SM id, end, 0}
+        unsigned long long t;
+        uint32_t smid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        p.dbg[128 + 4 * blockIdx.x] = t;
+        p.dbg[129 + 4 * blockIdx.x] = smid;
+    }
     if (tid == 0) {
         mbar_init(&sm.bar_rkw, 1);
         mbar_init(&sm.bar_vg[0], 1);
@@ -240,6 +247,11 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         const uint64_t vgoff = (cb & 1) ? DOFF(CL * 128) : 0;   // V / G buffer of this chunk (v[1] - v[0] = g[1] - g[0] = 8 KB)
         const uint64_t dk_g = dk_g0 + vgoff, dk_v = dk_v0 + vgoff, dm_g = dm_g0 + vgoff;
         const int c_ts = cb;
+        // Programmatic dependent launch: the next kernel of the stream may become resident from the LAST chunk on.  (Its
+        // CTAs take whatever SMs this grid leaves free and sit in griddepcontrol.wait; triggered at the top of the kernel
+        // they kept every SM occupied for the whole launch, which locked concurrent kernels of other streams out -- the
+        // all-reduce of the training step did not overlap at all.)
+        if (cb == nchunks - 1) pdl_launch_dependents();
         WKV6_TS(64, 0);
         // staging tiles of the previous chunk have been read (they alias operand tiles that are rewritten after the next
         // CTA-wide barrier).  The store thread is warp 7 lane 0: it issues no MMAs, so this wait delays nobody.
@@ -801,6 +813,12 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         const int hc = tid >> 5, cc = tid & 31;
         const float g = sm.gured[4 * hc + 0][cc] + sm.gured[4 * hc + 1][cc] + sm.gured[4 * hc + 2][cc] + sm.gured[4 * hc + 3][cc];
         reinterpret_cast<__nv_bfloat16*>(D.gu)[(size_t)b * p.C + h * N + tid] = __float2bfloat16_rn(g);
+    }
+    if (p.dbg && tid == 0 && blockIdx.x < 1024) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.dbg[130 + 4 * blockIdx.x] = t;
+        p.dbg[131 + 4 * blockIdx.x] = 0;
     }
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
 }

@@ -68,3 +68,25 @@ if rows:
     print(f"ctas {len(rows)} span {t_max - t_min} ns; cta duration min/med/max {durs[0]}/{durs[len(durs)//2]}/{durs[-1]} ns; "
           f"SMs used {len(per_sm)}, SMs with 2 CTAs {sum(1 for v in per_sm.values() if len(v) >= 2)}, overlapping in time {overlap2}; "
           f"last start {starts[-1]} ns")
+
+
+# ---- per-CTA timeline of the backward chunk kernel (persistent balanced grid)
+pk.bi_forward_raw(f, r_, ckpt=ck)
+flush.fill_(4)
+torch.cuda.synchronize()
+L.wkv6_b200_debug_trace(0, None)
+L.wkv6_b200_debug_trace(1, None)
+pk.bi_backward_raw(f, r_, a["gy"], b["gy"], ckpt=ck)
+torch.cuda.synchronize()
+L.wkv6_b200_debug_trace_ctas(cb)
+rows = [(cb[4 * i], cb[4 * i + 1], cb[4 * i + 2], cb[4 * i + 3]) for i in range(1024) if cb[4 * i] and cb[4 * i + 2]]
+if rows:
+    t_min = min(r[0] for r in rows); t_max = max(r[2] for r in rows)
+    durs = sorted(r[2] - r[0] for r in rows)
+    print(f"bwd: {len(rows)} CTAs on {len(set(r[1] for r in rows))} SMs, kernel span {t_max - t_min} ns; CTA ns min/med/max "
+          f"{durs[0]}/{durs[len(durs)//2]}/{durs[-1]}; mean {sum(durs)//len(durs)}; start spread {max(r[0] for r in rows) - t_min} ns; "
+          f"end spread {t_max - min(r[2] for r in rows)} ns; hand-over wait ns max {max(r[3] for r in rows)} "
+          f"sum {sum(r[3] for r in rows)}")
+    full = [(cb[4 * i + 2] - cb[4 * i], i, cb[4 * i + 1]) for i in range(1024) if cb[4 * i] and cb[4 * i + 2]]
+    print("bwd per CTA (blockIdx:smid:ns):", " ".join(f"{i}:{sm_}:{d_}" for d_, i, sm_ in sorted(full, key=lambda x: x[1])))
+L.wkv6_b200_debug_trace(0, None)
