@@ -321,7 +321,7 @@ def run_b200(args):
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / reps
 
-    def timed(step, steps, warmup, sampler=None):
+    def timed(step, steps, warmup, sampler=None, tag=None):
         """`steps` steps, the timed region bracketed by a barrier + synchronize on both sides and by CUDA events on the
         launching stream, nothing but the kernel launches inside (an event record between two launches serialises them
         and defeats the dependent-launch overlap).  Returns ms/step (max over ranks) and the launches in the region."""
@@ -332,10 +332,14 @@ def run_b200(args):
         if sampler:
             sampler.start()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if tag:
+            torch.cuda.nvtx.range_push(tag)       # lets `ncu --nvtx --nvtx-include <tag>/` pick a launch of this very region
         t0.record()
         for _ in range(steps):
             step()
         t1.record()
+        if tag:
+            torch.cuda.nvtx.range_pop()
         barrier()
         return allmax(t0.elapsed_time(t1)) / steps, pk.launch_count() - n0
 
@@ -362,7 +366,7 @@ def run_b200(args):
 
     # ---- headline: the training step (fwd with checkpoint stores + bwd), configs[1] shape
     sampler = ClockSampler(local)
-    ms_step, launches = timed(train_step, args.steps, args.warmup, sampler)
+    ms_step, launches = timed(train_step, args.steps, args.warmup, sampler, tag="train_timed")
     t_end = time.time() + 1.5
     while time.time() < t_end and len(sampler.rows) < 6:     # a short timed region: keep the same load up until sampled
         train_step()
@@ -394,7 +398,7 @@ def run_b200(args):
 
     # ---- inference (configs[1] literally): the forward alone, no checkpoint stores
     def leg_infer():
-        ms, n = timed(infer_step, args.steps, args.warmup)
+        ms, n = timed(infer_step, args.steps, args.warmup, tag="infer_timed")
         return {"metric": "encoder frames/s (bi-WKV6 fwd)", "value": world * B * T / (ms * 1e-3), "unit": "frames/s",
                 "ms_per_step": ms, "steps": args.steps, "gpu_launches": n,
                 "roofline": roof("wkv6_fwd_chunk_lean_kernel: bidirectional forward, one launch per block", fwd_bytes, ms / NL, "fwd")}

@@ -100,6 +100,10 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         p.dbg[128 + 4 * blockIdx.x] = t;
         p.dbg[129 + 4 * blockIdx.x] = smid;
     }
+    // Programmatic dependent launch: the next kernel of the stream may become resident from here on (its prologue overlaps
+    // this kernel's tail).  Triggering later, e.g. at the last chunk, was tried: the instruction inside the chunk loop costs
+    // 50 R2UR / 120 instructions of code generation and 2.5 us per launch.
+    pdl_launch_dependents();
     if (tid == 0) {
         mbar_init(&sm.bar_rkw, 1);
         mbar_init(&sm.bar_vg[0], 1);
@@ -247,11 +251,6 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         const uint64_t vgoff = (cb & 1) ? DOFF(CL * 128) : 0;   // V / G buffer of this chunk (v[1] - v[0] = g[1] - g[0] = 8 KB)
         const uint64_t dk_g = dk_g0 + vgoff, dk_v = dk_v0 + vgoff, dm_g = dm_g0 + vgoff;
         const int c_ts = cb;
-        // Programmatic dependent launch: the next kernel of the stream may become resident from the LAST chunk on.  (Its
-        // CTAs take whatever SMs this grid leaves free and sit in griddepcontrol.wait; triggered at the top of the kernel
-        // they kept every SM occupied for the whole launch, which locked concurrent kernels of other streams out -- the
-        // all-reduce of the training step did not overlap at all.)
-        if (cb == nchunks - 1) pdl_launch_dependents();
         WKV6_TS(64, 0);
         // staging tiles of the previous chunk have been read (they alias operand tiles that are rewritten after the next
         // CTA-wide barrier).  The store thread is warp 7 lane 0: it issues no MMAs, so this wait delays nobody.
