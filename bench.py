@@ -16,6 +16,9 @@ Beside the headline the same JSON line carries (each is a leg of `--legs`, all o
             block is queued (DDP's find_unused_parameters=True volume: a dropped direction contributes zeros)
   cfg5      configs[4]: fp32, B=1, T=90 000, d_model 1024, 16 heads, one bidirectional block, forward
   longform  configs[2]: 8 utterances x T=30 000 in total, sharded over the ranks (strong scaling), forward
+  conv      SURVEY 8f4: the Conformer ConvolutionModule that follows the time-mix in every layer (kernel 31, layer_norm,
+            swish) on configs[1]'s shape, fp32: the fused GLU + depthwise conv + LayerNorm + swish core against its
+            roofline, and the whole module (with its two pointwise GEMMs) against the reference's eager op sequence
   ref_cuda  the reference's own CUDA kernels (oracle/_ref/libwkv6_ref.so = wkv6_cuda.cu unmodified) on the same GPU
   cpu       the CPU port of the reference kernels (oracle/) on the host cores, bounded sample
 
@@ -36,7 +39,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 CFG = dict(layers=12, C=512, H=8, B=16, T=750)
-ALL_LEGS = ("infer", "e2e", "cfg4", "cfg5", "longform", "ref_cuda", "cpu")
+ALL_LEGS = ("infer", "e2e", "cfg4", "cfg5", "longform", "conv", "ref_cuda", "cpu")
 TMIX_PARAMS_PER_DIRECTION = 1249792       # SURVEY App. C at C = 512: 5C + 128C + 128C + C + 64C + 64C + C + 4C^2 + 2C
 KERNEL_SOURCES = ("wkv6_chunk_lean.cu", "wkv6_chunk_bwd.cu", "wkv6_fwd_tiles.cuh", "wkv6_umma.cuh", "wkv6_common.cuh")
 
@@ -689,7 +692,57 @@ def run_b200(args):
                 "what": "fwd+bwd through the C ABI from pinned host slabs: H2D of r,k,v,w,u,gy and D2H of gr,gk,gv,gw,gu of both "
                         "directions inside the timed region, every block"}
 
+    # ---- ConvolutionModule (wenet/transformer/convolution.py:89-144), kernel 31 / layer_norm / swish, fp32
+    def leg_conv():
+        from paper_accurate_fast_cheap_b200.convolution import ConvolutionModule, convmod_core
+        K = 31
+        torch.manual_seed(5)
+        mod = ConvolutionModule(C, K, torch.nn.SiLU(), "layer_norm", False, True).to(dev).eval()
+        gz = torch.Generator(device=dev).manual_seed(99 + rank)
+        zs = [torch.randn(B, T, 2 * C, device=dev, generator=gz) for _ in range(4)]      # 4 x 49 MB: every launch reads cold z
+        xs = [torch.randn(B, T, C, device=dev, generator=gz) for _ in range(4)]
+        dw, nm = mod.depthwise_conv, mod.norm
+        cur = [0]
+
+        def core():
+            cur[0] = (cur[0] + 1) & 3
+            return convmod_core(zs[cur[0]], dw.weight, dw.bias, nm.weight, nm.bias, nm.eps, T, (K - 1) // 2)
+
+        def core_eager():          # the reference's ops between the two pointwise convolutions (:121-137), on [B, 2C, T]
+            cur[0] = (cur[0] + 1) & 3
+            z = zs[cur[0]].transpose(1, 2)
+            y = dw(torch.nn.functional.glu(z, dim=1)).transpose(1, 2)
+            return torch.nn.functional.silu(nm(y)).transpose(1, 2)
+
+        def module(fused):
+            cur[0] = (cur[0] + 1) & 3
+            with torch.no_grad():
+                return mod(xs[cur[0]]) if fused else mod._forward_eager(xs[cur[0]], torch.ones((0, 0, 0), dtype=torch.bool, device=dev),
+                                                                          torch.zeros((0, 0, 0), device=dev))
+        with torch.no_grad():
+            for fn in (core, core_eager):
+                fn(); fn()
+            module(True); module(False)
+            reps = max(5, min(args.steps, 50))
+            n0 = pk.launch_count()
+            t_core = allmax(region(core, reps))
+            n_l = pk.launch_count() - n0
+            t_eager = allmax(region(core_eager, reps))
+            t_mod, t_mod_eager = allmax(region(lambda: module(True), reps)), allmax(region(lambda: module(False), reps))
+        nbytes = B * T * 3 * C * 4
+        ach = nbytes / (t_core * 1e-3) / 1e9
+        return {"metric": "encoder frames/s (ConvolutionModule core: GLU + depthwise k=31 + LayerNorm + swish)",
+                "workload": f"configs[1] shape, one block: B={B} x T={T}, d_model={C}, kernel 31, fp32", "unit": "frames/s",
+                "value": world * B * T / (t_core * 1e-3), "ms_per_block": t_core, "gpu_launches": n_l,
+                "eager_ops_ms_per_block": t_eager, "speedup_vs_eager_ops": t_eager / t_core,
+                "module_ms_per_block": t_mod, "module_eager_ms_per_block": t_mod_eager,
+                "roofline": {"bound": "hbm", "kernel": "convmod_core_kernel<float, 31>", "achieved": ach, "peak": pk_["hbm_gbs"],
+                             "unit": "GB/s", "frac": ach / pk_["hbm_gbs"], "peak_source": how,
+                             "alg_bytes_per_launch": nbytes, "kernel_ms": t_core,
+                             "note": "algorithmic bytes: read z [B,T,2C], write y [B,T,C]"}}
+
     leg("infer", leg_infer)
+    leg("conv", leg_conv)
     leg("cfg4", leg_cfg4)
     leg("longform", leg_longform)
     leg("cfg5", leg_cfg5)

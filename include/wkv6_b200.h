@@ -142,6 +142,21 @@ int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void
                        const void* maa_k, const void* maa_v, const void* maa_w, int reverse, void* xxx, void* xr, void* xk,
                        void* xv, void* xw, void* stream);
 
+/* The block that follows the time-mix in every encoder layer: the bandwidth-bound middle of the Conformer
+ * ConvolutionModule, wenet/transformer/convolution.py:123-137 -- GLU, depthwise Conv1d (+ bias), LayerNorm over the
+ * channels, swish -- in one pass over the [B][T][C] layout (no transposes), between the two pointwise convolutions
+ * (GEMMs, :122 and :138, which stay library calls):
+ *   g[t][c]   = z[t][c] * sigmoid(z[t][C + c])                          z: [B][Tin][2C] in `dtype` = pointwise_conv1(x)
+ *   d[t][c]   = dw_bias[c] + sum_k dw_weight[c][k] * g[t + k - left][c]  (g = 0 outside [0, Tin))
+ *   y[t][c]   = swish(ln_weight[c] * (d[t][c] - mean_t) / sqrt(var_t + eps) + ln_bias[c]),   t in [0, Tout)
+ * Non-causal (reference padding (K-1)/2): Tin = Tout = T, left = (K-1)/2.  Causal with the lorder = K-1 frames of left
+ * context (zeros or the cache) already in front of x (:111-117): Tin = T + K - 1, Tout = T, left = 0.
+ * dw_weight [C][K], dw_bias [C] (may be NULL), ln_weight / ln_bias [C]: fp32.  K is 15 or 31; C % 64 == 0, 64 <= C <= 1024;
+ * fp32 arithmetic for either I/O dtype. */
+int wkv6_b200_convmod_core(int dtype, int B, int Tin, int Tout, int C, int K, int left, const void* z,
+                           const float* dw_weight, const float* dw_bias, const float* ln_weight, const float* ln_bias,
+                           float eps, void* y, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

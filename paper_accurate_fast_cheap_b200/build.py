@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libwkv6_b200.so")
 TORCH_LIB = os.path.join(HERE, "libwkv6_b200_torch.so")
-CUDA_SOURCES = ["wkv6_scan.cu", "wkv6_chunk_lean.cu", "wkv6_chunk_bwd.cu", "wkv6_tmix.cu", "wkv6_capi.cu"]
+CUDA_SOURCES = ["wkv6_scan.cu", "wkv6_chunk_lean.cu", "wkv6_chunk_bwd.cu", "wkv6_tmix.cu", "convmod.cu", "wkv6_capi.cu"]
 HEADERS = ["wkv6_common.cuh", "wkv6_scan.cuh", "wkv6_umma.cuh", "wkv6_fwd_tiles.cuh", "../../include/wkv6_b200.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]

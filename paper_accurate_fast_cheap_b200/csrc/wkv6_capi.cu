@@ -452,4 +452,17 @@ int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void
     return cuda_fail(launch_tmix_mix(dtype, B, T, C, x, x_edge, m, maa, reverse, out, (cudaStream_t)stream), "wkv6 tmix_mix launch");
 }
 
+int wkv6_b200_convmod_core(int dtype, int B, int Tin, int Tout, int C, int K, int left, const void* z, const float* dw_weight,
+                           const float* dw_bias, const float* ln_weight, const float* ln_bias, float eps, void* y, void* stream) {
+    if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
+    if (B < 0 || Tin < 0 || Tout < 0 || left < 0) return fail(WKV6_E_BADARG, "convmod_core: bad sizes B=%d Tin=%d Tout=%d left=%d", B, Tin, Tout, left);
+    if (C < 64 || C > 1024 || C % 64) return fail(WKV6_E_BADSHAPE, "convmod_core: C (%d) must be a multiple of 64 in [64, 1024]", C);
+    if (K != 15 && K != 31) return fail(WKV6_E_BADSHAPE, "convmod_core: kernel size %d (15 and 31 are built)", K);
+    if (B == 0 || Tout == 0) return 0;
+    if (!z || !y || !dw_weight || !ln_weight || !ln_bias || !aligned16(z) || !aligned16(y))
+        return fail(WKV6_E_BADARG, "convmod_core: NULL or misaligned pointer");
+    return cuda_fail(launch_convmod_core(dtype, B, Tin, Tout, C, K, left, z, dw_weight, dw_bias, ln_weight, ln_bias, eps, y,
+                                         (cudaStream_t)stream), "convmod_core launch");
+}
+
 }  // extern "C"

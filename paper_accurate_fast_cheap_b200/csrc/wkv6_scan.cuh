@@ -55,6 +55,8 @@ int launch_seg_scan(const Params& q, cudaStream_t st);
 int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
 int launch_bwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05; needs DirArgs::ckpt
+int launch_convmod_core(int dtype, int B, int Tin, int Tout, int C, int K, int left, const void* z, const float* dw_w,
+                        const float* dw_b, const float* ln_w, const float* ln_b, float eps, void* y, cudaStream_t st);
 int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out, cudaStream_t st);
 
 void count_launch(int n);
