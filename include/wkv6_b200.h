@@ -142,6 +142,25 @@ int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void
                        const void* maa_k, const void* maa_v, const void* maa_w, int reverse, void* xxx, void* xr, void* xk,
                        void* xv, void* xw, void* stream);
 
+/* The two LayerNorms of a bidirectional block's epilogue (RWKV_Tmix_x060c.ln_x of each direction, model.py:323), written
+ * side by side: out[row] = [ ln_f(y_f[row]) || ln_b(y_b[row]) ], out is [rows][2C].  With it the two output projections,
+ * the add and the /2 of rwkv_wrapper_bidirectional.py:44-56 are ONE GEMM out x [W_f ; W_b]^T / 2 (library call).
+ * y_*, weights / biases [C] and out in `dtype`; C % 8 == 0, C <= 2048; statistics in fp32. */
+int wkv6_b200_ln_pair_cat(int dtype, long long rows, int C, const void* y_f, const void* y_b, const void* w_f, const void* b_f,
+                          const void* w_b, const void* b_b, float eps, void* out, void* stream);
+
+/* Backward of one stage of wkv6_b200_tmix_mix (training: the fused prologue with autograd on).  With xx = shift(x) - x:
+ *   stage 1 (m == NULL): g0 = gradient of xxx, maa0 = maa_x;   stage 2 (m != NULL): g0..g3 = gradients of xr, xk, xv, xw,
+ *   maa0..maa3 = maa_r, maa_k, maa_v, maa_w, m as in the forward.
+ *   gx   [B][T][C]    = gradient w.r.t. x through this stage (sum over the stage's outputs, including the shifted use of x)
+ *   gm   [4][B][T][C] = gradient w.r.t. m (stage 2; may be NULL)
+ *   gmaa [1 or 4][C]  = gradient w.r.t. the maa vectors, fp32, ACCUMULATED with atomics: zero-fill before the call
+ * x_edge of the forward is treated as a constant.  fp32 arithmetic, one rounding per stored value (the reference's eager
+ * autograd rounds after every elementwise op). */
+int wkv6_b200_tmix_mix_backward(int dtype, int B, int T, int C, const void* x, const void* m, const void* maa0, const void* maa1,
+                                const void* maa2, const void* maa3, const void* g0, const void* g1, const void* g2,
+                                const void* g3, int reverse, void* gx, void* gm, float* gmaa, void* stream);
+
 /* The block that follows the time-mix in every encoder layer: the bandwidth-bound middle of the Conformer
  * ConvolutionModule, wenet/transformer/convolution.py:123-137 -- GLU, depthwise Conv1d (+ bias), LayerNorm over the
  * channels, swish -- in one pass over the [B][T][C] layout (no transposes), between the two pointwise convolutions

@@ -16,7 +16,7 @@ ALGO_AUTO, ALGO_SCAN, ALGO_CHUNK = 0, 1, 2
 SYMBOLS = (
     "wkv6_b200_abi_version", "wkv6_b200_last_error", "wkv6_b200_launch_count", "wkv6_b200_set_algo",
     "wkv6_b200_get_algo", "wkv6_b200_debug_trace", "wkv6_b200_forward_scratch_bytes", "wkv6_b200_debug_trace_ctas", "wkv6_b200_checkpoint_bytes", "wkv6_b200_forward", "wkv6_b200_backward_workspace_bytes", "wkv6_b200_backward",
-    "wkv6_b200_bi_forward", "wkv6_b200_bi_backward", "wkv6_b200_combine", "wkv6_b200_tmix_mix", "wkv6_b200_convmod_core",
+    "wkv6_b200_bi_forward", "wkv6_b200_bi_backward", "wkv6_b200_combine", "wkv6_b200_tmix_mix", "wkv6_b200_tmix_mix_backward", "wkv6_b200_ln_pair_cat", "wkv6_b200_convmod_core",
 )
 
 _lib = None
@@ -63,6 +63,10 @@ def lib() -> ctypes.CDLL:
     L.wkv6_b200_combine.restype = _i
     L.wkv6_b200_tmix_mix.argtypes = [_i] * 4 + [_vp] * 8 + [_i] + [_vp] * 6
     L.wkv6_b200_tmix_mix.restype = _i
+    L.wkv6_b200_tmix_mix_backward.argtypes = [_i] * 4 + [_vp] * 10 + [_i] + [_vp] * 4
+    L.wkv6_b200_tmix_mix_backward.restype = _i
+    L.wkv6_b200_ln_pair_cat.argtypes = [_i, ctypes.c_longlong, _i] + [_vp] * 6 + [ctypes.c_float, _vp, _vp]
+    L.wkv6_b200_ln_pair_cat.restype = _i
     L.wkv6_b200_convmod_core.argtypes = [_i] * 7 + [_vp] * 5 + [ctypes.c_float, _vp, _vp]
     L.wkv6_b200_convmod_core.restype = _i
     _lib = L

@@ -452,6 +452,35 @@ int wkv6_b200_tmix_mix(int dtype, int B, int T, int C, const void* x, const void
     return cuda_fail(launch_tmix_mix(dtype, B, T, C, x, x_edge, m, maa, reverse, out, (cudaStream_t)stream), "wkv6 tmix_mix launch");
 }
 
+int wkv6_b200_ln_pair_cat(int dtype, long long rows, int C, const void* y_f, const void* y_b, const void* w_f, const void* b_f,
+                          const void* w_b, const void* b_b, float eps, void* out, void* stream) {
+    if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
+    if (rows < 0 || C <= 0 || C % 8 || C > 2048) return fail(WKV6_E_BADARG, "ln_pair_cat: bad shape rows=%lld C=%d (C %% 8 == 0, C <= 2048)", rows, C);
+    if (rows == 0) return 0;
+    const void* ptrs[7] = {y_f, y_b, w_f, b_f, w_b, b_b, out};
+    for (const void* q : ptrs)
+        if (!q || !aligned16(q)) return fail(WKV6_E_BADARG, "ln_pair_cat: NULL or misaligned pointer");
+    return cuda_fail(launch_ln_pair_cat(dtype, rows, C, y_f, y_b, w_f, b_f, w_b, b_b, eps, out, (cudaStream_t)stream), "wkv6 ln_pair_cat launch");
+}
+
+int wkv6_b200_tmix_mix_backward(int dtype, int B, int T, int C, const void* x, const void* m, const void* maa0, const void* maa1,
+                                const void* maa2, const void* maa3, const void* g0, const void* g1, const void* g2,
+                                const void* g3, int reverse, void* gx, void* gm, float* gmaa, void* stream) {
+    if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);
+    if (B < 0 || T < 0 || C <= 0 || C % 8) return fail(WKV6_E_BADARG, "tmix_mix_backward: bad shape B=%d T=%d C=%d (C %% 8 == 0)", B, T, C);
+    if (B == 0 || T == 0) return 0;
+    const void* maa[4] = {maa0, maa1, maa2, maa3};
+    const void* g[4] = {g0, g1, g2, g3};
+    const int np = m ? 4 : 1;
+    if (!x || !gx || !gmaa || !aligned16(x) || !aligned16(gx) || (m && !aligned16(m)) || (gm && !aligned16(gm)))
+        return fail(WKV6_E_BADARG, "tmix_mix_backward: NULL/misaligned x, gx, gmaa, m or gm");
+    for (int i = 0; i < np; i++)
+        if (!maa[i] || !g[i] || !aligned16(maa[i]) || !aligned16(g[i]))
+            return fail(WKV6_E_BADARG, "tmix_mix_backward: NULL/misaligned maa or gradient %d", i);
+    return cuda_fail(launch_tmix_mix_bwd(dtype, B, T, C, x, m, maa, g, reverse, gx, gm, gmaa, (cudaStream_t)stream),
+                     "wkv6 tmix_mix_backward launch");
+}
+
 int wkv6_b200_convmod_core(int dtype, int B, int Tin, int Tout, int C, int K, int left, const void* z, const float* dw_weight,
                            const float* dw_bias, const float* ln_weight, const float* ln_bias, float eps, void* y, void* stream) {
     if (dtype != WKV6_DTYPE_BF16 && dtype != WKV6_DTYPE_F32) return fail(WKV6_E_BADDTYPE, "unknown dtype %d", dtype);

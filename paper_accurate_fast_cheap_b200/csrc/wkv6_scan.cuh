@@ -55,6 +55,10 @@ int launch_seg_scan(const Params& q, cudaStream_t st);
 int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
 int launch_bwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05; needs DirArgs::ckpt
+int launch_tmix_mix_bwd(int dtype, int B, int T, int C, const void* x, const void* m, const void* const* maa, const void* const* g,
+                        int reverse, void* gx, void* gm, float* gmaa, cudaStream_t st);
+int launch_ln_pair_cat(int dtype, long long rows, int C, const void* y_f, const void* y_b, const void* w_f, const void* b_f,
+                       const void* w_b, const void* b_b, float eps, void* out, cudaStream_t st);
 int launch_convmod_core(int dtype, int B, int Tin, int Tout, int C, int K, int left, const void* z, const float* dw_w,
                         const float* dw_b, const float* ln_w, const float* ln_b, float eps, void* y, cudaStream_t st);
 int launch_combine(int dtype, size_t n, const void* a, const void* b, float scale, int round_sum, float* out, cudaStream_t st);

@@ -192,6 +192,103 @@ def combine(a: torch.Tensor, b: Optional[torch.Tensor], scale: float = 0.5, roun
     return out
 
 
+def ln_pair_cat(y_f: torch.Tensor, y_b: torch.Tensor, ln_f, ln_b) -> torch.Tensor:
+    """[ln_f(y_f) || ln_b(y_b)] as one kernel: y_* [B,T,C] -> [B,T,2C] (include/wkv6_b200.h: wkv6_b200_ln_pair_cat).
+    ln_f / ln_b: the two nn.LayerNorm modules (model.py:262, one per direction).  No autograd graph is recorded."""
+    assert y_f.is_cuda and y_f.is_contiguous() and y_b.is_contiguous() and y_f.shape == y_b.shape and y_f.dtype == y_b.dtype
+    B, T, C = y_f.shape
+    out = torch.empty((B, T, 2 * C), device=y_f.device, dtype=y_f.dtype)
+    prm = [t.detach().to(y_f.dtype).contiguous() for t in (ln_f.weight, ln_f.bias, ln_b.weight, ln_b.bias)]
+    assert ln_f.eps == ln_b.eps
+    with torch.cuda.device(y_f.device):
+        _lib.check(_lib.lib().wkv6_b200_ln_pair_cat(_dtype_code(y_f), B * T, C, _p(y_f), _p(y_b), *[_p(t) for t in prm],
+                                                    float(ln_f.eps), _p(out), _stream(y_f)))
+    return out
+
+
+def _tmix_fwd(x, x_edge, m, maa, reverse, nout):
+    B, T, C = x.shape
+    L, dt, st = _lib.lib(), _dtype_code(x), _stream(x)
+    outs = [torch.empty_like(x) for _ in range(nout)]
+    with torch.cuda.device(x.device):
+        if m is None:
+            _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), _p(x_edge), None, _p(maa[0]), None, None, None, None, int(reverse),
+                                            _p(outs[0]), None, None, None, None, st))
+        else:
+            _lib.check(L.wkv6_b200_tmix_mix(dt, B, T, C, _p(x), _p(x_edge), _p(m), None, *[_p(t) for t in maa], int(reverse),
+                                            None, *[_p(o) for o in outs], st))
+    return outs
+
+
+def _tmix_bwd(x, m, maa, grads, reverse):
+    """gx, gm (or None), gmaa [NP, C] fp32 of one stage (include/wkv6_b200.h: wkv6_b200_tmix_mix_backward)."""
+    B, T, C = x.shape
+    L, dt, st = _lib.lib(), _dtype_code(x), _stream(x)
+    npairs = 4 if m is not None else 1
+    grads = [(torch.zeros_like(x) if g is None else g.contiguous()) for g in grads]
+    gx = torch.empty_like(x)
+    gm = torch.empty_like(m) if m is not None else None
+    gmaa = torch.zeros((npairs, C), device=x.device, dtype=torch.float32)
+    pad = [None] * (4 - npairs)
+    with torch.cuda.device(x.device):
+        _lib.check(L.wkv6_b200_tmix_mix_backward(dt, B, T, C, _p(x), _p(m), *[_p(t) for t in maa], *pad, *[_p(g) for g in grads], *pad,
+                                                 int(reverse), _p(gx), _p(gm), _p(gmaa), st))
+    return gx, gm, gmaa
+
+
+def _flat(t, like):
+    return t.detach().reshape(-1).to(like.dtype).contiguous()
+
+
+class TmixStage1(torch.autograd.Function):
+    """xxx = x + (shift(x) - x) * maa_x  (model.py:272-275) as one kernel, with its backward."""
+
+    @staticmethod
+    def forward(ctx, x, maa_x, reverse, x_edge):
+        ctx.reverse, ctx.pshape, ctx.pdtype = bool(reverse), maa_x.shape, maa_x.dtype
+        mx = _flat(maa_x, x)
+        ctx.save_for_backward(x, mx)
+        return _tmix_fwd(x, x_edge, None, [mx], reverse, 1)[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        x, mx = ctx.saved_tensors
+        gx, _, gmaa = _tmix_bwd(x, None, [mx], [g], ctx.reverse)
+        return gx, gmaa[0].to(ctx.pdtype).view(ctx.pshape), None, None
+
+
+class TmixStage2(torch.autograd.Function):
+    """x_c = x + (shift(x) - x) * (maa_c + m_c), c in r, k, v, w  (model.py:280-287) as one kernel, with its backward."""
+
+    @staticmethod
+    def forward(ctx, x, m, maa_r, maa_k, maa_v, maa_w, reverse, x_edge):
+        ctx.reverse, ctx.pshape, ctx.pdtype = bool(reverse), maa_r.shape, maa_r.dtype
+        maa = [_flat(t, x) for t in (maa_r, maa_k, maa_v, maa_w)]
+        ctx.save_for_backward(x, m, *maa)
+        return tuple(_tmix_fwd(x, x_edge, m, maa, reverse, 4))
+
+    @staticmethod
+    def backward(ctx, g_r, g_k, g_v, g_w):
+        x, m, *maa = ctx.saved_tensors
+        gx, gm, gmaa = _tmix_bwd(x, m, maa, [g_r, g_k, g_v, g_w], ctx.reverse)
+        gp = [gmaa[i].to(ctx.pdtype).view(ctx.pshape) for i in range(4)]
+        return gx, gm, gp[0], gp[1], gp[2], gp[3], None, None
+
+
+def tmix_mix_autograd(x: torch.Tensor, maa_x, maa_rkvw, w1, w2, reverse: bool = False, x_edge: Optional[torch.Tensor] = None):
+    """tmix_mix with gradients: the two elementwise stages are autograd Functions on the fused kernels (forward and
+    backward), the LoRA GEMMs in between are torch ops.  Returns x_r, x_k, x_v, x_w."""
+    assert x.is_cuda and x.dim() == 3
+    x = x.contiguous()
+    B, T, C = x.shape
+    if x_edge is not None:
+        x_edge = x_edge.detach().to(x.dtype).reshape(B, C).contiguous()
+    xxx = TmixStage1.apply(x, maa_x, reverse, x_edge)
+    m = torch.tanh(xxx.view(B * T, C) @ w1).view(B * T, 4, -1).transpose(0, 1)
+    m = torch.bmm(m, w2).contiguous()                                    # [4, B*T, C]
+    return TmixStage2.apply(x, m, *maa_rkvw, reverse, x_edge)
+
+
 def tmix_mix(x: torch.Tensor, maa_x: torch.Tensor, maa_rkvw, w1: torch.Tensor, w2: torch.Tensor, reverse: bool = False,
              x_edge: Optional[torch.Tensor] = None):
     """Token shift + the five `maa` mixes of RWKV_Tmix_x060c.forward (model.py:270-289) with the two elementwise

@@ -69,11 +69,12 @@ class RWKV_Tmix_x060c(nn.Module):
         `x_edge` [B,C]: the frame beyond the edge the shift looks across (streaming: last frame of the previous piece);
         None = zeros, as at the start of an utterance."""
         B, T, C = x.size()
-        if x.is_cuda and not torch.is_grad_enabled() and x.dtype in (torch.bfloat16, torch.float32) and C % 8 == 0:
-            # inference: the elementwise stages run fused (ops.tmix_mix, bit-exact with the eager ops below)
-            xr, xk, xv, ww = ops.tmix_mix(x.contiguous(), self.time_maa_x,
-                                          (self.time_maa_r, self.time_maa_k, self.time_maa_v, self.time_maa_w),
-                                          self.time_maa_rkvw_w1, self.time_maa_rkvw_w2, reverse, x_edge)
+        if x.is_cuda and x.dtype in (torch.bfloat16, torch.float32) and C % 8 == 0:
+            # the elementwise stages run fused (forward bit-exact with the eager ops below; with autograd on, their backward
+            # is one kernel per stage as well: ops.TmixStage1 / TmixStage2), the LoRA GEMMs in between are torch ops
+            xr, xk, xv, ww = ops.tmix_mix_autograd(x, self.time_maa_x,
+                                                   (self.time_maa_r, self.time_maa_k, self.time_maa_v, self.time_maa_w),
+                                                   self.time_maa_rkvw_w1, self.time_maa_rkvw_w2, reverse, x_edge)
             w = self.time_decay + torch.tanh(ww @ self.time_decay_w1) @ self.time_decay_w2
             return (self.receptance(xr).contiguous(), self.key(xk).contiguous(), self.value(xv).contiguous(),
                     w.contiguous())
@@ -164,13 +165,38 @@ class RWKV_TmixWrapper(nn.Module):
         return torch.zeros(batch, self.n_head * self.head_size * self.head_size + self.n_embd, dtype=torch.float32, device=device)
 
 
-def _bi_block(fwd: RWKV_Tmix_x060c, bwd: RWKV_Tmix_x060c, x: torch.Tensor, run_l2r: bool, run_r2l: bool):
-    """Both Tmix blocks on the same un-flipped x: prologues, ONE scan launch, epilogues.  Returns (out_f, out_b) in
-    x's dtype at natural time positions; None for a direction that did not run."""
+def _bi_scan(fwd: RWKV_Tmix_x060c, bwd: RWKV_Tmix_x060c, x: torch.Tensor, run_l2r: bool, run_r2l: bool):
+    """Both Tmix blocks on the same un-flipped x: prologues and ONE scan launch.  Returns (y_f, y_b), None where dropped."""
     set_f = (*fwd.prologue(x, reverse=False), fwd.time_faaaa) if run_l2r else None
     set_b = (*bwd.prologue(x, reverse=True), bwd.time_faaaa) if run_r2l else None
-    y_f, y_b = autograd.bi_wkv6(set_f if run_l2r else set_b, set_b if run_r2l else set_f, run_l2r, run_r2l)
+    return autograd.bi_wkv6(set_f if run_l2r else set_b, set_b if run_r2l else set_f, run_l2r, run_r2l)
+
+
+def _bi_block(fwd: RWKV_Tmix_x060c, bwd: RWKV_Tmix_x060c, x: torch.Tensor, run_l2r: bool, run_r2l: bool):
+    """_bi_scan + the two epilogues.  Returns (out_f, out_b) in x's dtype at natural time positions; None for a direction
+    that did not run."""
+    y_f, y_b = _bi_scan(fwd, bwd, x, run_l2r, run_r2l)
     return (fwd.epilogue(y_f) if run_l2r else None), (bwd.epilogue(y_b) if run_r2l else None)
+
+
+def _fused_epilogue_ok(x: torch.Tensor) -> bool:
+    return x.is_cuda and not torch.is_grad_enabled() and x.dtype in (torch.bfloat16, torch.float32) and x.shape[-1] % 8 == 0
+
+
+def _bi_block_mean(owner: nn.Module, fwd: RWKV_Tmix_x060c, bwd: RWKV_Tmix_x060c, x: torch.Tensor) -> torch.Tensor:
+    """(F(x) + G(x)) / 2 of both directions with the epilogue as ONE GEMM (inference): the two ln_x write side by side
+    (ops.ln_pair_cat) and [ln_f(y_f) || ln_b(y_b)] x [W_f ; W_b]^T / 2 replaces two output projections, the add and the
+    halving (model.py:323-324 twice + rwkv_wrapper_bidirectional.py:48).  Result in x's dtype; the sum is formed in the
+    GEMM's fp32 accumulator and rounded once (the reference rounds each projection, then the sum)."""
+    y_f, y_b = _bi_scan(fwd, bwd, x, True, True)
+    z = ops.ln_pair_cat(y_f, y_b, fwd.ln_x, bwd.ln_x)
+    wf, wb = fwd.output.weight, bwd.output.weight
+    key = (wf.data_ptr(), wf._version, wb.data_ptr(), wb._version, wf.dtype, wf.device)
+    cached = getattr(owner, "_wcat_half", None)
+    if cached is None or cached[0] != key:
+        cached = (key, (torch.cat([wf.detach(), wb.detach()], dim=1) * 0.5).contiguous())     # [C_out, 2C]; x 0.5 is exact
+        owner._wcat_half = cached
+    return F.linear(z, cached[1])
 
 
 class _BiBase(nn.Module):
@@ -197,6 +223,9 @@ class RWKV_TmixWrapper_bidirectional(_BiBase):
 
     def forward(self, query, key=None, value=None, mask=_EMPTY_MASK, pos_emb=_EMPTY_POS, cache=_EMPTY_CACHE):
         x = query.to(dtype=torch.bfloat16) if self.do_bfloat16 else query
+        if _fused_epilogue_ok(x):
+            out = _bi_block_mean(self, *self._blocks(), x)
+            return (out.float() if self.do_bfloat16 else out.to(query.dtype)), cache
         o_f, o_b = _bi_block(*self._blocks(), x, True, True)
         # the reference adds and halves in x's dtype, then casts (:48-54): round_sum reproduces the bf16 rounding
         out = autograd.combine(o_f, o_b, 0.5, round_sum=self.do_bfloat16, out_float=True)
@@ -246,6 +275,8 @@ class RWKV_TmixWrapper_bidirectional_direction_dropout(_BiBase):
         run_f, run_b = self._directions()
         qd = query.dtype
         x = query.to(dtype=torch.bfloat16) if self.do_bfloat16 else query      # inner wrappers cast per direction
+        if run_f and run_b and _fused_epilogue_ok(x):
+            return _bi_block_mean(self, *self._blocks(), x).to(qd), cache
         o_f, o_b = _bi_block(*self._blocks(), x, run_f, run_b)
         if run_f and run_b:
             # inner wrappers hand back query-dtype tensors; the reference averages those (fp32 when the encoder is)
