@@ -19,6 +19,9 @@ Beside the headline the same JSON line carries (each is a leg of `--legs`, all o
   conv      SURVEY 8f4: the Conformer ConvolutionModule that follows the time-mix in every layer (kernel 31, layer_norm,
             swish) on configs[1]'s shape, fp32: the fused GLU + depthwise conv + LayerNorm + swish core against its
             roofline, and the whole module (with its two pointwise GEMMs) against the reference's eager op sequence
+  module    the attention-slot MODULES (the call wenet's encoder layer makes): 12 x RWKV_TmixWrapper_bidirectional, inference,
+            and 12 x ..._direction_dropout_both, training step, bf16, B=16 (resp. 8) x T=750 -- this package against the
+            reference's formulation on the same GPU (eager prologue / epilogue ops, its CUDA kernels, flips, add, cast)
   ref_cuda  the reference's own CUDA kernels (oracle/_ref/libwkv6_ref.so = wkv6_cuda.cu unmodified) on the same GPU
   cpu       the CPU port of the reference kernels (oracle/) on the host cores, bounded sample
 
@@ -39,7 +42,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 CFG = dict(layers=12, C=512, H=8, B=16, T=750)
-ALL_LEGS = ("infer", "e2e", "cfg4", "cfg5", "longform", "conv", "ref_cuda", "cpu")
+ALL_LEGS = ("infer", "e2e", "cfg4", "cfg5", "longform", "conv", "module", "ref_cuda", "cpu")
 TMIX_PARAMS_PER_DIRECTION = 1249792       # SURVEY App. C at C = 512: 5C + 128C + 128C + C + 64C + 64C + C + 4C^2 + 2C
 KERNEL_SOURCES = ("wkv6_chunk_lean.cu", "wkv6_chunk_bwd.cu", "wkv6_fwd_tiles.cuh", "wkv6_umma.cuh", "wkv6_common.cuh")
 
@@ -741,8 +744,118 @@ def run_b200(args):
                              "alg_bytes_per_launch": nbytes, "kernel_ms": t_core,
                              "note": "algorithmic bytes: read z [B,T,2C], write y [B,T,C]"}}
 
+    # ---- module level: what wenet's encoder layer calls (self_attn(x, x, x, mask, pos_emb, cache)), 12 blocks
+    def leg_module():
+        import paper_accurate_fast_cheap_b200.wrappers as W
+        so = os.path.join(ROOT, "oracle", "_ref", "libwkv6_ref.so")
+        ref = ctypes.CDLL(so) if os.path.exists(so) else None
+        vp = lambda t: ctypes.c_void_p(t.data_ptr())
+
+        class RefWKV(torch.autograd.Function):           # model.py:108-159 on the reference's own kernels
+            @staticmethod
+            def forward(ctx, r, k, v, w, u):
+                Bq, Tq, Cq = r.shape
+                ctx.save_for_backward(r, k, v, w, u)
+                y = torch.empty_like(r)
+                assert ref.wkv6_ref_forward(0, Bq, Tq, Cq, Cq // 64, vp(r), vp(k), vp(v), vp(w), vp(u), vp(y)) == 0
+                return y
+
+            @staticmethod
+            def backward(ctx, gy):
+                r, k, v, w, u = ctx.saved_tensors
+                Bq, Tq, Cq = r.shape
+                gy = gy.contiguous()
+                g4 = [torch.empty_like(r) for _ in range(4)]
+                gu = torch.empty((Bq, Cq), device=r.device, dtype=r.dtype)
+                assert ref.wkv6_ref_backward(0, Bq, Tq, Cq, Cq // 64, vp(r), vp(k), vp(v), vp(w), vp(u), vp(gy), *[vp(t) for t in g4], vp(gu)) == 0
+                return (*g4, torch.sum(gu, 0).view(Cq // 64, 64))
+
+        def ref_tmix(blk, x):                            # RWKV_Tmix_x060c.forward as the reference writes it (model.py:270-325)
+            Bq, Tq, Cq = x.size()
+            xx = torch.nn.functional.pad(x[:, :-1], (0, 0, 1, 0)) - x
+            xxx = x + xx * blk.time_maa_x
+            xxx = torch.tanh(xxx @ blk.time_maa_rkvw_w1).view(Bq * Tq, 4, -1).transpose(0, 1)
+            xxx = torch.bmm(xxx, blk.time_maa_rkvw_w2).view(4, Bq, Tq, Cq)
+            mr, mk, mv, mw = xxx.unbind(dim=0)
+            r = blk.receptance(x + xx * (blk.time_maa_r + mr))
+            k = blk.key(x + xx * (blk.time_maa_k + mk))
+            v = blk.value(x + xx * (blk.time_maa_v + mv))
+            ww = x + xx * (blk.time_maa_w + mw)
+            w = blk.time_decay + torch.tanh(ww @ blk.time_decay_w1) @ blk.time_decay_w2
+            y = RefWKV.apply(r.contiguous(), k.contiguous(), v.contiguous(), w.contiguous(), blk.time_faaaa)
+            return blk.output(blk.ln_x(y))
+
+        def ref_bi(mod, x, run_f=True, run_b=True):      # rwkv_wrapper_bidirectional.py:43-56 / ..._dropout_both.py:53-99
+            xb = x.to(torch.bfloat16)
+            f, b = mod._blocks()
+            o_f = ref_tmix(f, xb) if run_f else None
+            o_b = torch.flip(ref_tmix(b, torch.flip(xb, [1])), [1]) if run_b else None
+            if run_f and run_b:
+                return ((o_f + o_b) / 2).float()
+            return (o_f if run_f else o_b).float()
+
+        torch.manual_seed(777)
+        infer_mods = [W.RWKV_TmixWrapper_bidirectional(64, C, NL, "v6", "bi", 4096, True, l).to(dev).eval() for l in range(NL)]
+        train_mods = [W.RWKV_TmixWrapper_bidirectional_direction_dropout_both(64, C, NL, "v6", "bi", 4096, True, l).to(dev).train()
+                      for l in range(NL)]
+        with torch.no_grad():                            # fresh modules have zero LoRA-A matrices: make every GEMM do real work
+            for m_ in infer_mods + train_mods:
+                for blk in m_._blocks():
+                    blk.time_maa_rkvw_w1.normal_(0, 0.02)
+                    blk.time_decay_w1.normal_(0, 0.02)
+        xg = torch.Generator(device=dev).manual_seed(31 + rank)
+        x16 = torch.randn(B, T, C, device=dev, generator=xg)
+        x8 = x16[:8].contiguous()
+        res = {"workload": f"12 attention-slot modules, d_model={C}, bf16 inside / fp32 interface, T={T}: inference B={B} "
+                           "(RWKV_TmixWrapper_bidirectional), training step B=8 (..._direction_dropout_both, p=0.2, same seeded draws)"}
+
+        # every block sees the same input (no residual stream / feed-forward between them here: chained, the 12 bare blocks
+        # amplify a bf16-rounding difference to O(1) and outputs could not be compared)
+        def infer_ours():
+            with torch.no_grad():
+                return torch.stack([m_(x16, x16, x16)[0] for m_ in infer_mods])
+
+        def infer_ref():
+            with torch.no_grad():
+                return torch.stack([ref_bi(m_, x16) for m_ in infer_mods])
+
+        def train_step(ours):
+            torch.manual_seed(4321)                      # both variants see the same Bernoulli sequence
+            h = x8.clone().requires_grad_(True)
+            loss = 0.0
+            for m_ in train_mods:
+                if ours:
+                    o = m_(h, h, h)[0]
+                else:
+                    run_f, run_b = m_._directions()
+                    o = ref_bi(m_, h, run_f, run_b)
+                loss = loss + o.float().square().mean()
+            loss.backward()
+            for m_ in train_mods:
+                m_.zero_grad(set_to_none=True)
+            return h.grad
+
+        reps = max(3, min(args.steps, 10))
+        a_ = infer_ours()
+        t_io = allmax(region(infer_ours, reps))
+        res["infer"] = {"ms_per_step": t_io, "frames_per_s": world * B * T / (t_io * 1e-3)}
+        g_o = train_step(True)
+        t_to = allmax(region(lambda: train_step(True), reps))
+        res["train"] = {"ms_per_step": t_to, "frames_per_s": world * 8 * T / (t_to * 1e-3)}
+        if ref is not None and rank == 0:
+            with torch.cuda.stream(torch.cuda.default_stream()):     # the reference's launchers use the legacy default stream
+                b_ = infer_ref()
+                t_ir = region(infer_ref, reps)
+                g_r = train_step(False)
+                t_tr = region(lambda: train_step(False), max(2, reps // 2))
+            rel = lambda p_, q_: float((p_.double() - q_.double()).abs().max() / q_.double().abs().max())
+            res["infer"].update({"reference_formulation_ms": t_ir, "speedup": t_ir / t_io, "max_rel_diff_of_outputs": rel(a_, b_)})
+            res["train"].update({"reference_formulation_ms": t_tr, "speedup": t_tr / t_to, "max_rel_diff_of_input_grads": rel(g_o, g_r)})
+        return res
+
     leg("infer", leg_infer)
     leg("conv", leg_conv)
+    leg("module", leg_module)
     leg("cfg4", leg_cfg4)
     leg("longform", leg_longform)
     leg("cfg5", leg_cfg5)
