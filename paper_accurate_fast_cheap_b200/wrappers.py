@@ -329,3 +329,47 @@ def install(class_utils=None) -> None:
         except Exception:
             return
     class_utils.WENET_ATTENTION_CLASSES.update(WENET_ATTENTION_CLASSES_B200)
+
+
+class GraphedInference:
+    """Replays the attention-slot modules of an encoder as ONE CUDA graph (inference, fixed [B, T, C] shape).
+
+    Eagerly, a bidirectional block is ~45 launches of which the scan is one: at configs[1]'s size the host cannot issue
+    them as fast as the B200 retires them (7.1 ms per 12 blocks against ~2 ms of kernel time).  Every entry point of
+    libwkv6_b200.so is capturable (no synchronisation, no allocation; launches go to the current stream), so the whole
+    stack is captured once and replayed:
+
+        g = GraphedInference(modules, example_x)      # modules: list of RWKV_TmixWrapper* in eval mode
+        outs = g(x)                                   # list of per-module outputs for this x (static buffers: copy to keep)
+
+    `chain=True` feeds every module the previous module's output (as a bare stack of blocks); the default gives every
+    module the same x, which is how an encoder layer calls it (its feed-forward / convolution modules run in between).
+    """
+
+    def __init__(self, modules, example_x: torch.Tensor, chain: bool = False, warmup: int = 2):
+        assert example_x.is_cuda, "GraphedInference: CUDA tensors only"
+        self.modules, self.chain = list(modules), chain
+        self.x = example_x.clone()
+        side = torch.cuda.Stream(device=example_x.device)
+        side.wait_stream(torch.cuda.current_stream(example_x.device))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(warmup):                    # first calls opt in to shared memory sizes, build cuBLAS handles, ...
+                self._run()
+        torch.cuda.current_stream(example_x.device).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.outs = self._run()
+
+    def _run(self):
+        outs, h = [], self.x
+        for m in self.modules:
+            o = m(h, h, h)[0]
+            outs.append(o)
+            if self.chain:
+                h = o
+        return outs
+
+    def __call__(self, x: torch.Tensor):
+        self.x.copy_(x)
+        self.graph.replay()
+        return self.outs

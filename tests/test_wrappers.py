@@ -122,3 +122,22 @@ def test_wrappers_have_no_cpu_scan():
     x = torch.randn(1, 8, 64)
     with pytest.raises(Exception):
         m(x, x, x)
+
+
+@pytest.mark.gpu
+def test_graphed_inference_replays_the_modules():
+    """The whole attention-slot stack as one CUDA graph: every C-ABI entry point is capturable; replay == eager, bit for bit."""
+    import paper_accurate_fast_cheap_b200 as pk
+    torch.manual_seed(11)
+    mods = [pk.RWKV_TmixWrapper_bidirectional(64, 128, 12, "v6", "bi", 2048, True, l).cuda().eval() for l in range(3)]
+    mods.append(pk.RWKV_TmixWrapper(64, 128, 12, "v6", "bi", 2048, True, 5).cuda().eval())
+    x1, x2 = torch.randn(2, 70, 128, device="cuda"), torch.randn(2, 70, 128, device="cuda")
+    g = pk.GraphedInference(mods, x1)
+    n0 = pk.launch_count()
+    for x in (x1, x2, x1):
+        outs = [o.clone() for o in g(x)]
+        with torch.no_grad():
+            want = [m(x, x, x)[0] for m in mods]
+        for a, b in zip(outs, want):
+            assert torch.equal(a, b)
+    assert pk.launch_count() > n0                        # the eager reference calls launched; replays do not go through the ABI
