@@ -581,7 +581,33 @@ def run_b200(args):
                                                   p(scratch) if nb else None, nb, stream))
         lms, n = timed(lstep, 3, 2)
         nbytes = 2 * 5 * LB * LT * C * 2
-        return {"metric": "encoder frames/s (bi-WKV6 fwd)", "value": world * LB * LT / (lms * 1e-3), "unit": "frames/s",
+        # long-form fine-tuning shape (conf/rwkv/*FT-LFXL*.yaml: 50 000 input frames -> T' = 12 499), one utterance per GPU,
+        # fwd (checkpoints) + bwd of one block: both time-segmented (the reference's backward cannot run T > ctx_len at all)
+        FT = 12499
+        fsets = [[x[:1, :FT].contiguous() if x.dim() == 3 else x for x in s_] for s_ in lsets]
+        fgy = [torch.randn(1, FT, C, device=dev, generator=gl).to(dt) for _ in range(2)]
+        fy = [torch.empty(1, FT, C, device=dev, dtype=dt) for _ in range(2)]
+        fg = [[torch.empty(1, FT, C, device=dev, dtype=dt) for _ in range(4)] + [torch.empty(1, C, device=dev, dtype=dt)] for _ in range(2)]
+        fck = torch.empty((2, L.wkv6_b200_checkpoint_bytes(1, FT, C, H)), device=dev, dtype=torch.uint8)
+        fnb = L.wkv6_b200_forward_scratch_bytes(0, 1, FT, C, H, 2)
+        bnb = L.wkv6_b200_backward_scratch_bytes(0, 1, FT, C, H, 2)
+        fsc = torch.empty(max(fnb, bnb, 16), device=dev, dtype=torch.uint8)
+
+        def ft_step(seg):
+            ff, fb = fsets
+            _lib.check(L.wkv6_b200_bi_forward(0, 1, FT, C, H, *[p(x) for x in ff], None, p(fy[0]), None, p(fck[0]),
+                                              *[p(x) for x in fb], None, p(fy[1]), None, p(fck[1]), BOTH,
+                                              p(fsc) if seg else None, fnb if seg else 0, stream))
+            _lib.check(L.wkv6_b200_bi_backward(0, 1, FT, C, H,
+                                               *[p(x) for x in ff], None, p(fgy[0]), None, p(fck[0]), *[p(x) for x in fg[0]], None,
+                                               *[p(x) for x in fb], None, p(fgy[1]), None, p(fck[1]), *[p(x) for x in fg[1]], None,
+                                               BOTH, p(fsc) if seg else None, bnb if seg else 0, stream))
+        ft_seg, ft_n = timed(lambda: ft_step(True), 5, 2)
+        ft_plain, _ = timed(lambda: ft_step(False), 3, 1)
+        ft = {"workload": f"1 utterance x T={FT} per GPU, C=512, 8 heads, bf16, ONE block, fwd (checkpoints) + bwd, both directions",
+              "ms_per_block": ft_seg, "ms_per_block_one_cta_per_sequence": ft_plain, "launches_per_block": ft_n // 5,
+              "frames_per_s_per_block": world * FT / (ft_seg * 1e-3)}
+        return {"finetune_longform": ft,"metric": "encoder frames/s (bi-WKV6 fwd)", "value": world * LB * LT / (lms * 1e-3), "unit": "frames/s",
                 "workload": f"configs[2]: 8 utterances x T=30000 in total, {LB} per GPU, C=512, 8 heads, bf16, 12 blocks, fwd",
                 "scaling": "strong", "ms_per_step": lms, "steps": 3, "launches_per_block": n // (3 * NL),
                 "hbm_frac": nbytes / (lms / NL * 1e-3) / 1e9 / pk_["hbm_gbs"]}

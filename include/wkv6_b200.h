@@ -97,8 +97,15 @@ int wkv6_b200_forward(int dtype, int B, int T, int C, int H,
                       const float* s0, void* y, float* sT, void* ckpt, int reverse,
                       void* scratch, size_t scratch_bytes, void* stream);
 
-/* Bytes of scratch the backward entry points need (0 is possible). */
+/* Bytes of workspace the backward entry points need when they are given no checkpoints (0 is possible). */
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections);
+/* Time segmentation of the bf16 backward (optional), the counterpart of the forward's: with few, long sequences
+ * (directions * B * H <= 74, T >= 2048: long-form fine-tuning) and a workspace of at least this many bytes a backward that
+ * IS given checkpoints sweeps every sequence in 2..40 time segments over all SMs (four launches: segment-local reverse
+ * states, segment scan, gradients, gu reduction); same results to the dtype's tolerance.  Returns 0 for shapes that would
+ * not be segmented; wkv6_b200_backward_workspace_bytes() includes these bytes.  The reference cannot run these shapes at
+ * all: its backward indexes a ctx_len-sized array (wkv6_cuda.cu:207). */
+size_t wkv6_b200_backward_scratch_bytes(int dtype, int B, int T, int C, int H, int ndirections);
 
 int wkv6_b200_backward(int dtype, int B, int T, int C, int H,
                        const void* r, const void* k, const void* v, const void* w, const void* u,

@@ -223,6 +223,7 @@ static int run_forward(int dtype, int B, int T, int C, int H, const FwdSet* sets
 }
 
 extern "C" size_t wkv6_b200_backward_workspace_bytes(int, int, int, int, int, int);
+extern "C" size_t wkv6_b200_backward_scratch_bytes(int, int, int, int, int, int);
 
 static int run_backward(int dtype, int B, int T, int C, int H, const BwdSet* sets, const int* reverse, int nset,
                         void* ws, size_t ws_bytes, void* stream) {
@@ -289,7 +290,12 @@ static int run_backward(int dtype, int B, int T, int C, int H, const BwdSet* set
             e = launch_fwd_chunk(pf, (cudaStream_t)stream);
             if (e) return cuda_fail(e, "wkv6 checkpoint recompute launch");
         }
-        e = launch_bwd_chunk(p, (cudaStream_t)stream);
+        // few, long sequences: time-segmented sweep on the scratch behind the recomputed checkpoints (if any) in the workspace
+        const size_t soff = recompute ? cb * nset : 0;
+        e = -1;
+        if (ws && aligned16(ws) && ws_bytes > soff)
+            e = launch_bwd_chunk_segmented(p, reinterpret_cast<char*>(ws) + soff, ws_bytes - soff, (cudaStream_t)stream);
+        if (e < 0) e = launch_bwd_chunk(p, (cudaStream_t)stream);
         return cuda_fail(e, "wkv6 chunk backward launch");
     }
     const size_t per_dir = (size_t)B * H * N * sizeof(float);
@@ -330,7 +336,7 @@ using namespace wkv6;
 
 extern "C" {
 
-int wkv6_b200_abi_version(void) { return 3; }
+int wkv6_b200_abi_version(void) { return 4; }
 /* Debug: enable != 0 allocates a device buffer that CTA 0 of the chunk kernels fills with clock64() stamps (forward:
  * slots 0..31, backward: 64..95) and, from slot 128 on, every CTA < 1024 of the forward chunk kernel with
  * {globaltimer at start, SM id, globaltimer at end, 0}; `out` (host, 128 entries) receives the first 128 slots;
@@ -373,6 +379,14 @@ int wkv6_b200_forward(int dtype, int B, int T, int C, int H, const void* r, cons
     return run_forward(dtype, B, T, C, H, &s, &rv, 1, scratch, scratch_bytes, stream);
 }
 
+size_t wkv6_b200_backward_scratch_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
+    if (check_common(dtype, B, T, C, H) || B == 0 || T == 0 || ndirections <= 0 || !use_chunk(dtype, T)) return 0;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.B = B; p.T = T; p.C = C; p.H = H; p.ndir = ndirections;
+    return bwd_segment_scratch_bytes(p);
+}
+
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
     if (B <= 0 || H <= 0 || ndirections <= 0) return 0;
     size_t n = (size_t)ndirections * B * H * N * sizeof(float);                    /* hT  */
@@ -380,6 +394,7 @@ size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H,
         n += (size_t)ndirections * B * T * C * 2;                                  /* grlo (exact scan)            */
         const size_t c = (size_t)ndirections * ckpt_bytes(B, T, H);                /* checkpoints (chunk backward) */
         if (c > n) n = c;
+        n += wkv6_b200_backward_scratch_bytes(dtype, B, T, C, H, ndirections);     /* time-segmented sweep         */
     }
     return n;
 }

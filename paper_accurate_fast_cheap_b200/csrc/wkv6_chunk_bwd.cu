@@ -74,13 +74,19 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     // turns every UTCHMMA into a waterfall loop of R2UR broadcasts)
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int BH = p.B * p.H;
-    const int ds = blockIdx.x / BH;
-    const int bh = blockIdx.x - ds * BH;
+    // time-segmented launch (launch_bwd_chunk_segmented below): CTA = (sequence, segment), segments in PROCESSING order
+    // (segment 0 holds the chunks the reverse sweep visits first); unsegmented: nseg = 1
+    const int nseg = p.nseg > 1 ? p.nseg : 1;
+    const int seq = blockIdx.x / nseg, seg = blockIdx.x - seq * nseg;
+    const int ds = seq / BH;
+    const int bh = seq - ds * BH;
     const int b = bh / p.H, h = bh - b * p.H;
     const DirArgs& D = p.d[ds];
     const bool rev = D.reverse != 0;
     const int T = p.T;
     const int nchunks = (T + CL - 1) / CL;
+    const int cbeg = nseg > 1 ? seg * p.seg_chunks : 0;                 // this CTA sweeps chunks cbeg .. cbeg + nloc - 1
+    const int nloc = nseg > 1 ? min(p.seg_chunks, nchunks - cbeg) : nchunks;   // (processing order)
 
     // compact variant tiles: virtual base (row 0) of every variant inside sm.kt / sm.rp
     const int vbK[4] = {rev ? 12288 : 0, rev ? 10240 : 2048, 6144, rev ? 0 : 12288};   // Ktil(I): sub-blocks <= I
@@ -121,8 +127,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         // reverse-state load), not after it
         fence_proxy_async();
         pdl_wait();
-        if (nchunks > 0) {
-            const int q0 = rev ? 0 : nchunks - 1;          // tile of the chunk the reverse sweep starts with
+        if (nloc > 0) {
+            const int q0 = rev ? cbeg : nchunks - 1 - cbeg;   // tile of the chunk this CTA's reverse sweep starts with
             mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
             tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q0 * CL, b);
             tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q0 * CL, b);
@@ -131,7 +137,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             tma_load_3d(sm.v[0], &D.mv, &sm.bar_vg[0], h * N, q0 * CL, b);
             tma_load_3d(sm.g[0], &D.mg, &sm.bar_vg[0], h * N, q0 * CL, b);
             mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
-            tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1)) * N);
+            tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1 - cbeg)) * N);
         }
     }
     if (warp == 0) {
@@ -175,7 +181,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     // reverse state C^T[j][i]: j = frow + 8*hh, i = fcol + 8*rep + e  ->  cs[4*rep + 2*hh + e]
     float cs[16];
     {
-        const float* g0 = D.gsT ? D.gsT + (size_t)bh * N * N : nullptr;
+        // start of the sweep: the gradient into S_T; a later segment starts from what the segment scan left in its slot
+        const float* g0 = nseg > 1 ? p.seg_state + ((size_t)seq * nseg + seg) * N * N : D.gsT ? D.gsT + (size_t)bh * N * N : nullptr;
 #pragma unroll
         for (int rep = 0; rep < 4; rep++)
 #pragma unroll
@@ -217,7 +224,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 
     // Loads of the next chunk are issued as soon as their landing tiles are dead: r/k/w after the operand tiles are
     // built (r, k live on in registers), v/gy after the phase-2 MMAs, the checkpoint after the anchor sum.
-    auto tile_q = [&](int cb) { const int c = nchunks - 1 - cb; return rev ? nchunks - 1 - c : c; };
+    // (cb = local chunk counter of this CTA, 0 .. nloc - 1; cbeg + cb = chunk in the sequence's processing order)
+    auto tile_q = [&](int cb) { const int c = nchunks - 1 - (cbeg + cb); return rev ? nchunks - 1 - c : c; };
     auto issue_rkw = [&](int cb) {   // thread 0 only
         const int q = tile_q(cb);
         mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
@@ -233,7 +241,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     };
     auto issue_sp = [&](int cb) {
         mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
-        tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1 - cb)) * N);
+        tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1 - (cbeg + cb))) * N);
     };
     // (the loads of the first chunk were issued at the top of the prologue)
 
@@ -243,8 +251,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     constexpr uint32_t ID_KM64 = umma_idesc(0, 1, 64, 64);
     constexpr uint32_t ID_MM64 = umma_idesc(1, 1, 64, 64);
 
-    for (int cb = 0; cb < nchunks; cb++) {
-        const int c = nchunks - 1 - cb;                  // chunk index in the direction's own order
+    for (int cb = 0; cb < nloc; cb++) {
+        const int c = nchunks - 1 - (cbeg + cb);         // chunk index in the direction's own order
         const int q = rev ? nchunks - 1 - c : c;         // tile index in memory
         const int t0 = q * CL;
         const uint32_t par = cb & 1;
@@ -255,7 +263,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         // staging tiles of the previous chunk have been read (they alias operand tiles that are rewritten after the next
         // CTA-wide barrier).  The store thread is warp 7 lane 0: it issues no MMAs, so this wait delays nobody.
         if (tid == 224) tma_store_wait_read<0>();
-        if (tid == 0 && cb + 1 < nchunks) issue_vg(cb + 1);   // other V / G buffer: its readers finished last iteration
+        if (tid == 0 && cb + 1 < nloc) issue_vg(cb + 1);   // other V / G buffer: its readers finished last iteration
         if (warp < 3 && elect_one()) {
             // ---- MMA phase 1a: everything that needs no preprocessing (V, G, S_0, C are raw / carried tiles)
             mbar_wait(&sm.bar_vg[cb & 1], (cb >> 1) & 1);
@@ -438,7 +446,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 umma_commit(&sm.bar_mp);
             }
             __syncwarp();
-            if (tid == 0 && cb + 1 < nchunks) issue_rkw(cb + 1);
+            if (tid == 0 && cb + 1 < nloc) issue_rkw(cb + 1);
 #pragma unroll
             for (int r = 0; r < 4; r++) {       // R side: needed by the phase-2 MMAs only
                 const int off = sw_chunk(rows[r], cchunk) + coff;
@@ -691,7 +699,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         WKV6_TS(64, 12);
         __syncthreads();   // B4: xr / xk / hst / vg visible; all TMEM reads of this chunk done
         WKV6_TS(64, 13);
-        if (tid == 0 && cb + 1 < nchunks) issue_sp(cb + 1);   // S_0 tile is dead after the anchor sum
+        if (tid == 0 && cb + 1 < nloc) issue_sp(cb + 1);   // S_0 tile is dead after the anchor sum
 
         // ================= final epilogue (row-major): gr, gk, gu, gw
         {
@@ -797,7 +805,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 #pragma unroll
         for (int e = 0; e < 4; e++) sm.gured[warp][4 * cq + e] = gu4[e];
     }
-    if (D.gs0) {
+    if (D.gs0 && seg == nseg - 1) {                      // the sweep reached the sequence's first step
         float* g0 = D.gs0 + (size_t)bh * N * N;
 #pragma unroll
         for (int rep = 0; rep < 4; rep++)
@@ -811,7 +819,8 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     if (tid < N) {
         const int hc = tid >> 5, cc = tid & 31;
         const float g = sm.gured[4 * hc + 0][cc] + sm.gured[4 * hc + 1][cc] + sm.gured[4 * hc + 2][cc] + sm.gured[4 * hc + 3][cc];
-        reinterpret_cast<__nv_bfloat16*>(D.gu)[(size_t)b * p.C + h * N + tid] = __float2bfloat16_rn(g);
+        if (nseg > 1) p.seg_gu[((size_t)seq * nseg + seg) * N + tid] = g;      // summed by wkv6_bwd_seg_gu_kernel
+        else reinterpret_cast<__nv_bfloat16*>(D.gu)[(size_t)b * p.C + h * N + tid] = __float2bfloat16_rn(g);
     }
     if (p.dbg && tid == 0 && blockIdx.x < 1024) {
         unsigned long long t;
@@ -822,15 +831,287 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tbase) : "memory");
 }
 
-int launch_bwd_chunk(const Params& p, cudaStream_t st) {
+// ---------------------------------------------------------------------------------------------------------------
+// Time-segmented backward (few, long sequences: long-form fine-tuning, conf/rwkv/*FT-LFXL*.yaml -- one CTA per sequence
+// would leave most SMs idle and the sweep is serial in the reverse state C).  C is linear in itself across a run of chunks,
+// C_out = C_in * D + dC with D[j] = product of the run's per-step decays of key channel j, exactly like the forward state
+// (wkv6_chunk_lean.cu), so: pass 1 (wkv6_bwd_state_kernel, below) sweeps every segment from C = 0 in a state-only mode --
+// decays, the r 2^(A_p) tiles and the dC MMAs, about a fifth of a full chunk -- and leaves dC and D in the scratch;
+// wkv6_seg_scan_kernel turns them into every segment's starting C (from gsT); pass 2 is the normal kernel started from
+// those (segment parameters at the top of wkv6_bwd_chunk_kernel), with gu as per-segment partials that
+// wkv6_bwd_seg_gu_kernel sums.  Four launches; the forward states come from the checkpoints as always.
+struct BwdStateSmem {
+    alignas(1024) uint8_t raw_r[CL * 128];
+    alignas(1024) uint8_t raw_w[CL * 128];
+    alignas(1024) uint8_t g[2][CL * 128];
+    alignas(1024) uint8_t rst[CL * 128];
+    alignas(1024) uint8_t rst_lo[CL * 128];
+    float blocktot[4][N];
+    alignas(8) uint64_t bar_rw, bar_g[2], bar_m;
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(256) wkv6_bwd_state_kernel(const __grid_constant__ Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_bytes[];
+    BwdStateSmem& sm = *reinterpret_cast<BwdStateSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int BH = p.B * p.H, nseg = p.nseg;
+    const int seq = blockIdx.x / nseg, seg = blockIdx.x - seq * nseg;
+    const int ds = seq / BH, bh = seq - ds * BH;
+    const int b = bh / p.H, h = bh - b * p.H;
+    const DirArgs& D = p.d[ds];
+    const bool rev = D.reverse != 0;
+    const int T = p.T, nchunks = (T + CL - 1) / CL;
+    const int cbeg = seg * p.seg_chunks, nloc = min(p.seg_chunks, nchunks - cbeg);
+    auto tile_q = [&](int cb) { const int c = nchunks - 1 - (cbeg + cb); return rev ? nchunks - 1 - c : c; };
+    auto issue_rw = [&](int cb) {
+        const int q = tile_q(cb);
+        mbar_arrive_expect_tx(&sm.bar_rw, 2u * CL * 128);
+        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rw, h * N, q * CL, b);
+        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rw, h * N, q * CL, b);
+    };
+    auto issue_g = [&](int cb) {
+        mbar_arrive_expect_tx(&sm.bar_g[cb & 1], 1u * CL * 128);
+        tma_load_3d(sm.g[cb & 1], &D.mg, &sm.bar_g[cb & 1], h * N, tile_q(cb) * CL, b);
+    };
+    if (tid == 0) {
+        mbar_init(&sm.bar_rw, 1);
+        mbar_init(&sm.bar_g[0], 1);
+        mbar_init(&sm.bar_g[1], 1);
+        mbar_init(&sm.bar_m, 1);
+        fence_barrier_init();
+        tma_prefetch_desc(&D.mr); tma_prefetch_desc(&D.mw); tma_prefetch_desc(&D.mg);
+        fence_proxy_async();
+        if (nloc > 0) { issue_rw(0); issue_g(0); }
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // fragment coordinates (TMEM 16x256b.x4) and row-major coordinates: as in wkv6_bwd_chunk_kernel
+    const int qtr = warp & 3, half = warp >> 2;
+    const int frow = 16 * qtr + (lane >> 2);
+    const int fcol = 32 * half + 2 * (lane & 3);
+    const uint32_t lane_field = (uint32_t)(qtr * 32) << 16;
+    const int I = warp & 3, ch = warp >> 2;
+    const int cq = lane & 7, rg = lane >> 3;
+    const int c0 = 32 * ch + 4 * cq;
+    const int coff = (c0 & 7) * 2, cchunk = c0 >> 3;
+    float cs[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) cs[i] = 0.f;
+    float lsum0 = 0.f, lsum1 = 0.f;              // log2 of the decay product of key channels frow, frow + 8
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tDC = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
+    const uint64_t dm_rst = desc_mn(smem_u32(sm.rst)), dm_rstl = desc_mn(smem_u32(sm.rst_lo)), dm_g0 = desc_mn(smem_u32(sm.g[0]));
+    constexpr uint32_t ID_MM64 = umma_idesc(1, 1, 64, 64);
+
+    for (int cb = 0; cb < nloc; cb++) {
+        const int t0 = tile_q(cb) * CL;
+        const uint32_t par = cb & 1;
+        if (tid == 0 && cb + 1 < nloc) issue_g(cb + 1);
+        mbar_wait(&sm.bar_rw, par);
+        // decays, in-block cumulative sums, r 2^(A_p - a_I)  (phase 1 of the full kernel without its K side)
+        float ro[4][4];
+        {
+            float l2[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int pos = 16 * I + 4 * rg + r;
+                const int row = rev ? 63 - pos : pos;
+                const int off = sw_chunk(row, cchunk) + coff;
+                float w4[4];
+                ld4bf(sm.raw_r + off, ro[r]);
+                ld4bf(sm.raw_w + off, w4);
+                const bool valid = t0 + row < T;
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float x = ex2(w4[e] * kLog2e);
+                    l2[r][e] = valid ? fmaxf(-x * kLog2e, -kClampL2) : 0.f;
+                }
+            }
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                l2[1][e] += l2[0][e];
+                l2[2][e] += l2[1][e];
+                l2[3][e] += l2[2][e];
+            }
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                float x = l2[3][e];
+                float y = __shfl_up_sync(0xffffffffu, x, 8);
+                if (rg >= 1) x += y;
+                y = __shfl_up_sync(0xffffffffu, x, 16);
+                if (rg >= 2) x += y;
+                const float excl = x - l2[3][e];
+                if (rg == 3) sm.blocktot[I][c0 + e] = x;
+#pragma unroll
+                for (int r = 0; r < 4; r++) ro[r][e] *= ex2(excl + (r ? l2[r - 1][e] : 0.f));
+            }
+        }
+        __syncthreads();   // blocktot visible
+        {
+            float fst[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                float s_ = 0.f;
+#pragma unroll
+                for (int m = 0; m < 4; m++)
+                    if (m < I) s_ += sm.blocktot[m][c0 + e];
+                fst[e] = ex2(s_);
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int pos = 16 * I + 4 * rg + r;
+                const int row = rev ? 63 - pos : pos;
+                const int off = sw_chunk(row, cchunk) + coff;
+                float x4[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) x4[e] = ro[r][e] * fst[e];
+                st4bf_hilo(sm.rst + off, sm.rst_lo + off, x4);
+            }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();   // tiles complete; raw r / w are dead
+        if (tid == 0 && cb + 1 < nloc) issue_rw(cb + 1);
+        if (warp == 1 && elect_one()) {
+            tc_fence_after();
+            mbar_wait(&sm.bar_g[cb & 1], (cb >> 1) & 1);
+            const uint64_t dm_g = dm_g0 + ((cb & 1) ? (uint64_t)((CL * 128) >> 4) : 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tDC, dm_rst + (uint64_t)((ks * 2048) >> 4), dm_g + (uint64_t)((ks * 2048) >> 4), ID_MM64, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tDC, dm_rstl + (uint64_t)((ks * 2048) >> 4), dm_g + (uint64_t)((ks * 2048) >> 4), ID_MM64, 1);
+            umma_commit(&sm.bar_m);
+        }
+        __syncwarp();
+        mbar_wait(&sm.bar_m, par);
+        tc_fence_after();
+        {
+            float x[16];
+            tmem_ld_16x32(tDC + lane_field + 32 * half, x);
+            const float s0 = (sm.blocktot[0][frow] + sm.blocktot[1][frow]) + (sm.blocktot[2][frow] + sm.blocktot[3][frow]);
+            const float s1 = (sm.blocktot[0][frow + 8] + sm.blocktot[1][frow + 8]) + (sm.blocktot[2][frow + 8] + sm.blocktot[3][frow + 8]);
+            const float f0 = ex2(s0), f1 = ex2(s1);
+            lsum0 += s0;
+            lsum1 += s1;
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++) {
+                cs[4 * rep + 0] = fmaf(cs[4 * rep + 0], f0, x[4 * rep + 0]);
+                cs[4 * rep + 1] = fmaf(cs[4 * rep + 1], f0, x[4 * rep + 1]);
+                cs[4 * rep + 2] = fmaf(cs[4 * rep + 2], f1, x[4 * rep + 2]);
+                cs[4 * rep + 3] = fmaf(cs[4 * rep + 3], f1, x[4 * rep + 3]);
+            }
+        }
+        tc_fence_before();
+        __syncthreads();   // TMEM and blocktot reads of this chunk done
+    }
+    {
+        float* slot = p.seg_state + ((size_t)seq * nseg + seg) * N * N;       // [i][j], like gs0
+#pragma unroll
+        for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) slot[(fcol + 8 * rep + e) * N + frow + 8 * hh] = cs[4 * rep + 2 * hh + e];
+        if (half == 0 && (lane & 3) == 0) {
+            float* dec = p.seg_decay + ((size_t)seq * nseg + seg) * N;
+            dec[frow] = ex2(lsum0);
+            dec[frow + 8] = ex2(lsum1);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tDC) : "memory");
+}
+
+// gu[b][h*64 + c] = sum over the segments' partials (pass 2 of a time-segmented backward)
+__global__ void __launch_bounds__(64) wkv6_bwd_seg_gu_kernel(const __grid_constant__ Params p) {
+    const int BH = p.B * p.H, seq = blockIdx.x, ds = seq / BH, bh = seq - ds * BH;
+    const int b = bh / p.H, h = bh - b * p.H;
+    float g = 0.f;
+    for (int s_ = 0; s_ < p.nseg; s_++) g += p.seg_gu[((size_t)seq * p.nseg + s_) * N + threadIdx.x];
+    reinterpret_cast<__nv_bfloat16*>(p.d[ds].gu)[(size_t)b * p.C + h * N + threadIdx.x] = __float2bfloat16_rn(g);
+}
+
+constexpr int kMaxSegBwd = 40;   // = kMaxSeg of wkv6_seg_scan_kernel (wkv6_chunk_lean.cu)
+
+// Segments per sequence of a backward launch (0: unsegmented): one CTA per SM is resident, so segmentation pays when the
+// launch has at most 74 sequences; every segment at least 8 chunks long.
+static int pick_segments_bwd(const Params& p, size_t scratch_bytes, int* seg_chunks) {
+    const int nseq = p.ndir * p.B * p.H;
+    const int ntot = (p.T + CL - 1) / CL;
+    if (nseq <= 0 || nseq * 2 > 148 || ntot < 32) return 0;
+    int nseg = 148 / nseq;
+    if (nseg > ntot / 8) nseg = ntot / 8;
+    if (nseg > kMaxSegBwd) nseg = kMaxSegBwd;
+    if (nseg < 2) return 0;
+    const int sc = (ntot + nseg - 1) / nseg;
+    nseg = (ntot + sc - 1) / sc;
+    if ((size_t)nseq * nseg * (N * N + 2 * N) * sizeof(float) > scratch_bytes) return 0;
+    *seg_chunks = sc;
+    return nseg;
+}
+
+size_t bwd_segment_scratch_bytes(const Params& p) {
+    int sc = 0;
+    const int nseg = pick_segments_bwd(p, ~(size_t)0, &sc);
+    return nseg ? (size_t)p.ndir * p.B * p.H * nseg * (N * N + 2 * N) * sizeof(float) : 0;
+}
+
+static int launch_bwd_main(const Params& q, int grid, cudaStream_t st) {
     const size_t smem = sizeof(BwdChunkSmem) + 1024;
     cudaError_t e = opt_in_smem_once(wkv6_bwd_chunk_kernel, smem, 1);
     if (e != cudaSuccess) return (int)e;
-    Params q = p;
-    q.dbg = debug_trace_buffer();
-    e = launch_pdl(wkv6_bwd_chunk_kernel, dim3(q.ndir * q.B * q.H), dim3(256), smem, st, q);
+    e = launch_pdl(wkv6_bwd_chunk_kernel, dim3(grid), dim3(256), smem, st, q);
     count_launch(1);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
+}
+
+int launch_bwd_chunk(const Params& p, cudaStream_t st) {
+    Params q = p;
+    q.dbg = debug_trace_buffer();
+    q.nseg = 0;
+    return launch_bwd_main(q, q.ndir * q.B * q.H, st);
+}
+
+// -1: the shape is not segmented (or the scratch is missing / too small): the caller launches launch_bwd_chunk
+int launch_bwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    int sc = 0;
+    const int nseg = scratch ? pick_segments_bwd(p, scratch_bytes, &sc) : 0;
+    if (nseg == 0) return -1;
+    Params q = p;
+    q.dbg = debug_trace_buffer();
+    const int nseq = q.ndir * q.B * q.H;
+    q.nseg = nseg;
+    q.seg_chunks = sc;
+    q.seg_state = static_cast<float*>(scratch);
+    q.seg_decay = q.seg_state + (size_t)nseq * nseg * N * N;
+    q.seg_gu = q.seg_decay + (size_t)nseq * nseg * N;
+    const size_t smem1 = sizeof(BwdStateSmem) + 1024;
+    static std::atomic<unsigned long long> opted{0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (!(opted.load(std::memory_order_acquire) & (1ull << (dev & 63)))) {
+        if ((e = cudaFuncSetAttribute(wkv6_bwd_state_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1)) != cudaSuccess) return (int)e;
+        opted.fetch_or(1ull << (dev & 63), std::memory_order_release);
+    }
+    wkv6_bwd_state_kernel<<<dim3(nseq * nseg), dim3(256), smem1, st>>>(q);
+    count_launch(1);
+    if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
+    Params qs = q;                                   // the segment scan starts from "s0": here the gradient into S_T
+    for (int d = 0; d < q.ndir; d++) qs.d[d].s0 = q.d[d].gsT;
+    int rc = launch_seg_scan(qs, st);
+    if (rc) return rc;
+    if ((rc = launch_bwd_main(q, nseq * nseg, st))) return rc;
+    wkv6_bwd_seg_gu_kernel<<<dim3(nseq), dim3(64), 0, st>>>(q);
+    count_launch(1);
+    return (int)cudaGetLastError();
 }
 
 }  // namespace wkv6

@@ -40,6 +40,7 @@ struct Params {
     int seg_mode;                         // 1: pass 1 (local state + decay product of every segment), 2: pass 2 (outputs)
     float* seg_state;                     // [ndir][B*H][nseg][64 i][64 j]: pass 1 writes dS, the scan turns it into S_start
     float* seg_decay;                     // [ndir][B*H][nseg][64 j]: product of the per-step decays of the segment
+    float* seg_gu;                        // time-segmented backward: [ndir][B*H][nseg][64] partial gu of every segment
     unsigned long long* dbg;              // optional clock64() trace of one CTA (wkv6_b200_debug_trace), else null
 };
 
@@ -55,6 +56,8 @@ int launch_seg_scan(const Params& q, cudaStream_t st);
 int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
 int launch_bwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05; needs DirArgs::ckpt
+int launch_bwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
+size_t bwd_segment_scratch_bytes(const Params& p);
 int launch_tmix_mix_bwd(int dtype, int B, int T, int C, const void* x, const void* m, const void* const* maa, const void* const* g,
                         int reverse, void* gx, void* gm, float* gmaa, cudaStream_t st);
 int launch_ln_pair_cat(int dtype, long long rows, int C, const void* y_f, const void* y_b, const void* w_f, const void* b_f,

@@ -99,6 +99,16 @@ def wkv6_forward_raw(r, k, v, w, u, s0=None, reverse=False, want_state=False, ck
     return y, sT
 
 
+def _bwd_workspace_bytes(L, r, B, T, C, H, ndir, ckpt) -> int:
+    """Without checkpoints: everything the backward needs.  With checkpoints: only the scratch of the time-segmented sweep
+    (0 unless the launch is few, long sequences; `set_segmentation(False)` turns it off)."""
+    if ckpt is None:
+        return L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, ndir)
+    if not _segmentation or T < 2048:
+        return 0
+    return L.wkv6_b200_backward_scratch_bytes(_dtype_code(r), B, T, C, H, ndir)
+
+
 def wkv6_backward_raw(r, k, v, w, u, gy, s0=None, gsT=None, reverse=False, want_gs0=False, ckpt=None):
     """Returns gr, gk, gv, gw [B,T,C], gu [B,C] (per-batch partials, like the reference), gs0 or None."""
     B, T, C, H = _check_inputs(r, k, v, w, u, extra=(gy,))
@@ -108,7 +118,7 @@ def wkv6_backward_raw(r, k, v, w, u, gy, s0=None, gsT=None, reverse=False, want_
     gu = torch.empty((B, C), device=r.device, dtype=r.dtype)
     gs0 = torch.empty((B, H, HEAD_SIZE, HEAD_SIZE), device=r.device, dtype=torch.float32) if want_gs0 else None
     L = _lib.lib()
-    ws_bytes = 0 if ckpt is not None else L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, 1)
+    ws_bytes = _bwd_workspace_bytes(L, r, B, T, C, H, 1, ckpt)
     ws = torch.empty(ws_bytes, device=r.device, dtype=torch.uint8) if ws_bytes else None
     with torch.cuda.device(r.device):
         _lib.check(L.wkv6_b200_backward(_dtype_code(r), B, T, C, H, _p(r), _p(k), _p(v), _p(w), _p(u), _p(s0),
@@ -166,7 +176,7 @@ def bi_backward_raw(f, b, gy_f, gy_b, flags=_lib.BI_L2R | _lib.BI_R2L, s0_f=None
 
     of, ob = outs(run_f), outs(run_b)
     L = _lib.lib()
-    ws_bytes = 0 if ckpt is not None else L.wkv6_b200_backward_workspace_bytes(_dtype_code(ref[0]), B, T, C, H, 2)
+    ws_bytes = _bwd_workspace_bytes(L, ref[0], B, T, C, H, int(run_f) + int(run_b), ckpt)
     ck_f = ckpt[0] if (ckpt is not None and run_f) else None
     ck_b = ckpt[1] if (ckpt is not None and run_b) else None
     ws = torch.empty(ws_bytes, device=dev, dtype=torch.uint8) if ws_bytes else None

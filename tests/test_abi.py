@@ -25,7 +25,7 @@ def test_header_symbols_are_exported(built):
     L = built.lib()
     for s in declared:
         assert hasattr(L, s), s
-    assert L.wkv6_b200_abi_version() == 3
+    assert L.wkv6_b200_abi_version() == 4
 
 
 def test_argument_validation_without_gpu(built):
@@ -42,6 +42,12 @@ def test_argument_validation_without_gpu(built):
     assert L.wkv6_b200_backward_workspace_bytes(0, 2, 10, 128, 2, 2) == max(2 * 2 * 2 * 64 * 4 + 2 * 2 * 10 * 128 * 2,
                                                                             2 * L.wkv6_b200_checkpoint_bytes(2, 10, 128, 2))
     assert L.wkv6_b200_checkpoint_bytes(2, 130, 128, 2) == 2 * 2 * 3 * 64 * 64 * 2
+    # time-segmented backward: few, long sequences only; 148 one-CTA SMs, <= 40 segments, each >= 8 chunks
+    assert L.wkv6_b200_backward_scratch_bytes(0, 16, 750, 512, 8, 2) == 0
+    assert L.wkv6_b200_backward_scratch_bytes(1, 1, 30000, 512, 8, 2) == 0           # fp32: exact scan, not segmented
+    assert L.wkv6_b200_backward_scratch_bytes(0, 1, 12499, 512, 8, 2) == 16 * 9 * (64 * 64 + 128) * 4
+    assert L.wkv6_b200_backward_workspace_bytes(0, 1, 12499, 512, 8, 2) == (
+        2 * L.wkv6_b200_checkpoint_bytes(1, 12499, 512, 8) + L.wkv6_b200_backward_scratch_bytes(0, 1, 12499, 512, 8, 2))
     # time segmentation: only few, long sequences; the size is what the planner will use (<= 40 segments per sequence)
     assert L.wkv6_b200_forward_scratch_bytes(0, 16, 750, 512, 8, 2) == 0            # short
     assert L.wkv6_b200_forward_scratch_bytes(0, 16, 30000, 512, 8, 2) == 0          # 256 sequences: SMs are full

@@ -301,3 +301,83 @@ def test_two_devices_one_process():
         assert oracle.rel_err(y, y_ref) <= TOL[torch.bfloat16]
         for x, r_ in zip(o[:5], ref[:5]):
             assert oracle.rel_err(x, r_) <= TOL[torch.bfloat16]
+
+
+@pytest.mark.parametrize("B,T,H,flags,with_state", [
+    (1, 12499, 8, 3, False),     # FT-LFXL long-form fine-tuning shape: 50 000 input frames -> T' = 12 499, one utterance per GPU
+    (1, 2113, 2, 3, True),       # ragged T, initial state and gradient into the final state, 4 sequences x 4 segments
+    (2, 4100, 4, 2, True),       # one direction dropped: 8 sequences of the right-to-left set
+    (1, 2048, 1, 1, False),      # the shortest sequence that is segmented (32 chunks), left-to-right only
+])
+def test_time_segmented_backward(B, T, H, flags, with_state):
+    """Few, long sequences (long-form fine-tuning; the reference itself cannot run T > ctx_len backward, wkv6_cuda.cu:207):
+    with the scratch from wkv6_b200_backward_scratch_bytes the checkpointed backward runs time-segmented (segment-local
+    reverse states, segment scan, gradients, gu reduction: four launches); every gradient agrees with the
+    one-CTA-per-sequence launch and with the fp64 oracle."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import _lib, ops
+    a = _inputs(B, T, H, torch.bfloat16, with_state=with_state, seed=51)
+    b = _inputs(B, T, H, torch.bfloat16, with_state=with_state, seed=52, layer=7)
+    ga, gb = _cuda(a), _cuda(b)
+    f, r_ = tuple(ga[n] for n in "rkvwu"), tuple(gb[n] for n in "rkvwu")
+    run_f, run_b = bool(flags & 1), bool(flags & 2)
+    ndir = int(run_f) + int(run_b)
+    assert _lib.lib().wkv6_b200_backward_scratch_bytes(0, B, T, H * 64, H, ndir) > 0
+    ck = ops.checkpoint_buffer(ga["r"], 2)
+    pk.bi_forward_raw(f, r_, flags=flags, s0_f=ga.get("s0"), s0_b=gb.get("s0"), ckpt=ck)
+    kw = dict(flags=flags, s0_f=ga.get("s0"), s0_b=gb.get("s0"), gsT_f=ga.get("gsT"), gsT_b=gb.get("gsT"),
+              want_gs0=with_state, ckpt=ck)
+    gyf, gyb = (ga["gy"] if run_f else None), (gb["gy"] if run_b else None)
+    ops.set_segmentation(False)
+    try:
+        n0 = pk.launch_count()
+        of0, ob0 = pk.bi_backward_raw(f, r_, gyf, gyb, **kw)
+        assert pk.launch_count() - n0 == 1
+    finally:
+        ops.set_segmentation(True)
+    n0 = pk.launch_count()
+    of, ob = pk.bi_backward_raw(f, r_, gyf, gyb, **kw)
+    assert pk.launch_count() - n0 == 4, "expected state pass + segment scan + gradient pass + gu reduction"
+    nout = 6 if with_state else 5
+    for inp, o, o0, rev, run in ((a, of, of0, False, run_f), (b, ob, ob0, True, run_b)):
+        if not run:
+            assert o[0] is None
+            continue
+        for name, x, x0 in zip(("gr", "gk", "gv", "gw", "gu", "gs0"), o[:nout], o0[:nout]):
+            assert oracle.rel_err(x, x0.double()) <= 1e-2, (name, rev)      # same operands, fp32 state regrouped per segment
+        if B * T * H <= 70000:                                                # the fp64 oracle backward on the smaller cases
+            ref = oracle.bwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], inp["gy"], s0=inp.get("s0"),
+                             gsT=inp.get("gsT"), rev=rev, prec="f64")
+            for name, x, y in zip(("gr", "gk", "gv", "gw", "gu", "gs0"), o[:nout], ref[:nout]):
+                assert oracle.rel_err(x, y) <= TOL[torch.bfloat16], (name, rev)
+
+
+def test_time_segmented_backward_is_faster():
+    """The point of it: B = 1 x T = 12 499 x 8 heads, both directions (16 sequences on 148 SMs)."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import ops
+    B, T, H = 1, 12499, 8
+    ga, gb = _cuda(_inputs(B, T, H, torch.bfloat16, seed=61)), _cuda(_inputs(B, T, H, torch.bfloat16, seed=62, layer=7))
+    f, r_ = tuple(ga[n] for n in "rkvwu"), tuple(gb[n] for n in "rkvwu")
+    ck = ops.checkpoint_buffer(ga["r"], 2)
+    pk.bi_forward_raw(f, r_, ckpt=ck)
+
+    def ms(reps=3):
+        pk.bi_backward_raw(f, r_, ga["gy"], gb["gy"], ckpt=ck)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            pk.bi_backward_raw(f, r_, ga["gy"], gb["gy"], ckpt=ck)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    ops.set_segmentation(False)
+    try:
+        t_plain = ms()
+    finally:
+        ops.set_segmentation(True)
+    t_seg = ms()
+    print(f"\nbackward B=1 T=12499 H=8 both directions: one CTA per sequence {t_plain:.3f} ms, time-segmented {t_seg:.3f} ms")
+    assert t_seg < 0.5 * t_plain

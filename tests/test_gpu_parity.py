@@ -212,3 +212,62 @@ def test_matches_reference_cuda_golden_vectors(path):
         got = pk.wkv6_backward_raw(g["r"], g["k"], g["v"], g["w"], g["u"], g["gy"])
         for name, a in zip(("gr", "gk", "gv", "gw", "gu"), got[:5]):
             assert oracle.rel_err(a, c["outs"][name]) <= tol, name
+
+
+def test_scriptmodule_in_the_reference_style_runs_on_these_kernels():
+    """INTEGRATION level 1, run rather than asserted: a TorchScript ScriptModule written the way the reference's model.py is
+    (MyModule = torch.jit.ScriptModule, model.py:33-35; the WKV_6 autograd.Function calling torch.ops.wkv6.forward /
+    backward positionally on caller-allocated outputs, model.py:108-159) dispatches into libwkv6_b200.so after
+    install_ops(), forward and backward, bf16, on the GPU."""
+    pk = _pkg()
+    from paper_accurate_fast_cheap_b200 import wrappers
+    wrappers.install_ops()
+
+    class WKV_6_ref(torch.autograd.Function):            # the reference's function, restated with its call sites
+        @staticmethod
+        def forward(ctx, B: int, T: int, C: int, H: int, r, k, v, w, u):
+            ctx.B, ctx.T, ctx.C, ctx.H = B, T, C, H
+            ctx.save_for_backward(r, k, v, w, u)
+            y = torch.empty((B, T, C), device=r.device, dtype=torch.bfloat16, memory_format=torch.contiguous_format)
+            torch.ops.wkv6.forward(B, T, C, H, r, k, v, w, u, y)
+            return y
+
+        @staticmethod
+        def backward(ctx, gy):
+            B, T, C, H = ctx.B, ctx.T, ctx.C, ctx.H
+            r, k, v, w, u = ctx.saved_tensors
+            mk = lambda *s: torch.empty(s, device=gy.device, requires_grad=False, dtype=torch.bfloat16)
+            gr, gk, gv, gw, gu = mk(B, T, C), mk(B, T, C), mk(B, T, C), mk(B, T, C), mk(B, C)
+            torch.ops.wkv6.backward(B, T, C, H, r, k, v, w, u, gy.contiguous(), gr, gk, gv, gw, gu)
+            return (None, None, None, None, gr, gk, gv, gw, torch.sum(gu, 0).view(H, C // H))
+
+    class Block(torch.jit.ScriptModule):
+        def __init__(self, C: int, H: int):
+            super().__init__()
+            self.C, self.H = C, H
+            self.receptance = torch.nn.Linear(C, C, bias=False)
+
+        @torch.jit.script_method
+        def mix(self, x):
+            return self.receptance(x)
+
+        def forward(self, x, k, v, w, u):
+            r = self.mix(x)
+            return WKV_6_ref.apply(x.size(0), x.size(1), self.C, self.H, r.contiguous(), k, v, w, u)
+
+    inp = _inputs(2, 130, 2, torch.bfloat16)
+    g = _cuda(inp)
+    blk = Block(128, 2).to(DEV).to(torch.bfloat16)
+    with torch.no_grad():
+        blk.receptance.weight.copy_(torch.eye(128))       # r = x exactly: the oracle can check the result
+    leaves = {n: g[n].clone().requires_grad_(True) for n in "rkvwu"}
+    n0 = pk.launch_count()
+    y = blk(leaves["r"], leaves["k"], leaves["v"], leaves["w"], leaves["u"])
+    y.backward(g["gy"])
+    assert pk.launch_count() - n0 == 3                    # forward + (checkpoint recompute, sweep): the legacy ops keep no state
+    y_ref, _ = oracle.fwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], prec="f64")
+    ref = oracle.bwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], inp["gy"], prec="f64")
+    assert oracle.rel_err(y, y_ref) <= 2e-2
+    for n, want in zip("kvw", ref[1:4]):
+        assert oracle.rel_err(leaves[n].grad, want) <= 2e-2, n
+    assert oracle.rel_err(leaves["u"].grad, ref[4].sum(0).view(2, 64)) <= 2e-2
