@@ -425,13 +425,23 @@ def run_b200(args):
                 seq.append(_lib.BI_L2R if Bernoulli(0.8).sample((1,)) <= 0.5 else _lib.BI_R2L)
         torch.set_rng_state(cpu_state)
         NP = TMIX_PARAMS_PER_DIRECTION
-        PER_BUCKET = 4                                                    # blocks per bucket: 20 MB, DDP's bucket_cap_mb=25 scale
-        NBK = (NL + PER_BUCKET - 1) // PER_BUCKET
+        # buckets in the order the backward fills them (block 11 first), DDP-sized (bucket_cap_mb = 25: up to 5 blocks = 25 MB),
+        # shrinking towards the end: the bucket that closes last cannot overlap any backward work, so it is the smallest
+        BUCKET_BLOCKS = [5, 4, 2, 1] if NL == 12 else [NL]
+        NBK = len(BUCKET_BLOCKS)
+        first_block, bucket_of, pos_in = [], {}, {}
+        hi = NL
+        for k_, nb_ in enumerate(BUCKET_BLOCKS):
+            lo = hi - nb_
+            first_block.append(lo)
+            for l in range(lo, hi):
+                bucket_of[l], pos_in[l] = k_, l - lo
+            hi = lo
         gb = torch.Generator(device=dev).manual_seed(4242 + rank)
         # the surrounding model's gradients (GEMM / LoRA / LayerNorm weights) are outside the path: synthetic, fixed
         synth = [torch.randn(2 * NP, device=dev, generator=gb).mul_(1e-2).to(dt) for _ in range(NL)]
-        buckets = [torch.cat([synth[l] for l in range(k * PER_BUCKET, min(NL, (k + 1) * PER_BUCKET))]) for k in range(NBK)]
-        half_of = lambda l, d: buckets[l // PER_BUCKET][((l % PER_BUCKET) * 2 + d) * NP:((l % PER_BUCKET) * 2 + d + 1) * NP]
+        buckets = [torch.cat([synth[l] for l in range(first_block[k], first_block[k] + BUCKET_BLOCKS[k])]) for k in range(NBK)]
+        half_of = lambda l, d: buckets[bucket_of[l]][(pos_in[l] * 2 + d) * NP:(pos_in[l] * 2 + d + 1) * NP]
         zeroed = [[False, False] for _ in range(NL)]
         U_OFF = 5 * C + 2 * 128 * C + C + 2 * 64 * C                     # time_faaaa inside one direction's flat gradient
         comm = torch.cuda.Stream()
@@ -466,8 +476,8 @@ def run_b200(args):
                     elif not zeroed[l][d]:
                         half.zero_()
                         zeroed[l][d] = True
-                if collective and world > 1 and l % PER_BUCKET == 0:   # the bucket's last block (backward order) is done
-                    k_ = l // PER_BUCKET
+                if collective and world > 1 and pos_in[l] == 0:        # the bucket's last block (backward order) is done
+                    k_ = bucket_of[l]
                     evs[k_].record()
                     with torch.cuda.stream(comm):
                         comm.wait_event(evs[k_])
@@ -485,7 +495,7 @@ def run_b200(args):
         ms_without, _ = run(False)
         res = {"metric": "encoder frames/s (bi-WKV6 fwd+bwd, direction dropout, gradient all-reduce)",
                "workload": f"configs[3]: {B4} utterances x T={T} per GPU x {world} GPUs, 12 blocks, bf16, direction dropout p=0.2 "
-                           f"(dir_layer_drop_both), bf16 gradient buckets of {PER_BUCKET} blocks x 2 x 1 249 792",
+                           f"(dir_layer_drop_both), bf16 gradient buckets of {BUCKET_BLOCKS} blocks x 2 x 1 249 792",
                "value": world * B4 * T / (ms_with * 1e-3), "unit": "frames/s", "ms_per_step": ms_with,
                "ms_per_step_without_collective": ms_without, "steps": n4, "gpu_launches": n_l,
                "directions_run": {"both": seq[:n4 * NL].count(BOTH), "l2r_only": seq[:n4 * NL].count(_lib.BI_L2R),
@@ -509,7 +519,7 @@ def run_b200(args):
             dist.all_gather(allsig, sig)
             same = all(bool((s_ == allsig[0]).all()) for s_ in allsig)
             assert same, "gradient buckets differ across ranks after the all-reduce"
-            res.update({"collective": f"NCCL all_reduce(AVG) bf16, {NBK} buckets of {PER_BUCKET} blocks on a side stream, each issued "
+            res.update({"collective": f"NCCL all_reduce(AVG) bf16, {NBK} buckets of {BUCKET_BLOCKS} blocks on a side stream, each issued "
                                       "right after the backward launch of its last block", "allreduce_alone_ms": alone, "exposed_ms": exposed,
                         "overlap_fraction": max(0.0, min(1.0, 1.0 - exposed / max(alone, 1e-9))),
                         "buckets_identical_across_ranks": same})
