@@ -6,7 +6,7 @@ from .autograd import (BiWKV6, RUN_CUDA_RWKV6, RUN_CUDA_RWKV6_FP32, WKV6State, W
                        bi_wkv6, wkv6)
 from .wrappers import (RWKV_Tmix_x060c, RWKV_TmixWrapper, RWKV_TmixWrapper_bidirectional,  # noqa: F401
                        RWKV_TmixWrapper_bidirectional_direction_dropout,
-                       RWKV_TmixWrapper_bidirectional_direction_dropout_both, WENET_ATTENTION_CLASSES_B200, GraphedInference,
+                       RWKV_TmixWrapper_bidirectional_direction_dropout_both, WENET_ATTENTION_CLASSES_B200, GraphedInference, GraphedTraining,
                        install, install_ops)
 from .ops import (bi_backward_raw, bi_forward_raw, combine, wkv6_backward_raw, wkv6_forward_raw)  # noqa: F401
 from .convolution import ConvolutionModule, convmod_core, install_convolution  # noqa: F401
@@ -18,5 +18,5 @@ __all__ = [
     "RWKV_TmixWrapper_bidirectional_direction_dropout", "RWKV_TmixWrapper_bidirectional_direction_dropout_both",
     "WENET_ATTENTION_CLASSES_B200", "install", "install_ops",
     "load_torch_ops", "launch_count", "set_algo", "Wkv6Error",
-    "ConvolutionModule", "convmod_core", "install_convolution", "GraphedInference",
+    "ConvolutionModule", "convmod_core", "install_convolution", "GraphedInference", "GraphedTraining",
 ]

@@ -273,6 +273,10 @@ class RWKV_TmixWrapper_bidirectional_direction_dropout(_BiBase):
 
     def forward(self, query, key=None, value=None, mask=_EMPTY_MASK, pos_emb=_EMPTY_POS, cache=_EMPTY_CACHE):
         run_f, run_b = self._directions()
+        return self.forward_directions(query, run_f, run_b, cache)
+
+    def forward_directions(self, query, run_f: bool, run_b: bool, cache=_EMPTY_CACHE):
+        """forward() with the direction outcome given instead of drawn (GraphedTraining captures one graph per outcome)."""
         qd = query.dtype
         x = query.to(dtype=torch.bfloat16) if self.do_bfloat16 else query      # inner wrappers cast per direction
         if run_f and run_b and _fused_epilogue_ok(x):
@@ -373,3 +377,61 @@ class GraphedInference:
         self.x.copy_(x)
         self.graph.replay()
         return self.outs
+
+
+class _FixedDirections(nn.Module):
+    """x -> out of an attention-slot module with a fixed direction outcome (no host-side draw inside: capturable)."""
+
+    def __init__(self, module: nn.Module, run_f: bool, run_b: bool):
+        super().__init__()
+        self.module, self.run_f, self.run_b = module, run_f, run_b
+
+    def forward(self, x):
+        if hasattr(self.module, "forward_directions"):
+            return self.module.forward_directions(x, self.run_f, self.run_b)[0]
+        return self.module(x, x, x)[0]
+
+
+class GraphedTraining:
+    """Training step of ONE attention-slot module with forward and backward as CUDA graphs (fixed [B, T, C] shape).
+
+    The autograd Functions of this package (scan, fused prologue stages, combine) only launch kernels of libwkv6_b200.so and
+    torch ops on the current stream, so `torch.cuda.make_graphed_callables` captures a module's forward and its backward;
+    the eager training step is host-bound at configs[3]'s size (27 ms per 12 blocks against ~4 ms of kernel time, 11 ms
+    graphed).  Direction dropout is a HOST decision (one CPU Bernoulli draw per call, in the reference's order): one pair
+    of graphs per outcome -- both directions, L2R only, R2L only -- is captured when the object is built, and every call
+    draws exactly like the eager module and replays that outcome's graphs; a dropped direction's parameters get
+    no gradient (`allow_unused_input`), as in eager mode.  In eval mode the module is called directly.
+
+        slot = GraphedTraining(module, example_x)        # module.train(); example_x: [B, T, C] on the GPU
+        out = slot(x); loss(out).backward()              # out is a static buffer of the outcome's graph
+    """
+
+    def __init__(self, module: nn.Module, example_x: torch.Tensor, warmup: int = 3):
+        assert example_x.is_cuda, "GraphedTraining: CUDA tensors only"
+        self.module, self.warmup = module, warmup
+        self._example = example_x.detach().clone()
+        self._graphs = {}
+        # all outcomes are captured up front: a capture AFTER a replayed backward of another outcome's graph fails (the
+        # autograd engine then makes the legacy stream wait on the capturing stream for AccumulateGrad nodes that a live
+        # graph keeps alive)
+        if module.training:
+            outcomes = ((True, True), (True, False), (False, True)) if hasattr(module, "_directions") else ((True, True),)
+            for run in outcomes:
+                self._capture(run)
+
+    def _capture(self, run):
+        fixed = _FixedDirections(self.module, *run)
+        x = self._example.clone().requires_grad_(True)
+        g = torch.cuda.make_graphed_callables(fixed, (x,), num_warmup_iters=self.warmup, allow_unused_input=True)
+        self.module.zero_grad(set_to_none=True)          # the warm-up iterations ran real backward passes
+        self._graphs[run] = g
+        return g
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        m = self.module
+        if not m.training:
+            return m(x, x, x)[0]
+        run = tuple(m._directions()) if hasattr(m, "_directions") else (True, True)
+        g = self._graphs.get(run) or self._capture(run)
+        return g(x)

@@ -137,3 +137,45 @@ def test_module_gradients_match_reference_modules_gpu(path, monkeypatch):
     bf16 = bool(int(np.load(path)["meta"][2]))
     worst = _run_case(path, monkeypatch, "cuda:0", 3e-2 if bf16 else 1e-4, 5e-2 if bf16 else 3e-4)
     print(os.path.basename(path), "worst relative errors:", {k: f"{v:.2e}" for k, v in sorted(worst.items())})
+
+
+@pytest.mark.gpu
+def test_graphed_training_matches_eager_with_direction_dropout():
+    """GraphedTraining: forward and backward of a direction-dropout module as CUDA graphs, one pair per direction outcome,
+    drawn on the host exactly like the eager module.  Over a seeded sequence that takes all three outcomes, outputs and every
+    input / parameter gradient equal the eager step's bit for bit, and a dropped direction's parameters get no gradient."""
+    import paper_accurate_fast_cheap_b200 as pk
+    torch.manual_seed(21)
+    m = pk.RWKV_TmixWrapper_bidirectional_direction_dropout_both(64, 128, 12, "v6", "bi", 2048, True, 3).cuda().train()
+    with torch.no_grad():
+        for blk in m._blocks():
+            blk.time_maa_rkvw_w1.normal_(0, 0.05)
+            blk.time_decay_w1.normal_(0, 0.05)
+    xs = [torch.randn(2, 130, 128, device="cuda") for _ in range(2)]
+    gy = torch.randn(2, 130, 128, device="cuda")
+    slot = pk.GraphedTraining(m, xs[0])
+
+    def run(step_fn, seed):
+        torch.manual_seed(seed)
+        res = []
+        for i in range(10):
+            m.zero_grad(set_to_none=True)
+            x = xs[i & 1].clone().requires_grad_(True)
+            out = step_fn(x)
+            (out.float() * gy).sum().backward()
+            res.append((out.detach().clone(), x.grad.clone(), [None if p.grad is None else p.grad.clone() for p in m.parameters()]))
+        return res
+
+    eager = run(lambda x: m(x, x, x)[0], 5)
+    graphed = run(slot, 5)
+    outcomes = set()
+    for (o1, gx1, gp1), (o2, gx2, gp2) in zip(eager, graphed):
+        assert torch.equal(o1, o2) and torch.equal(gx1, gx2)
+        for a, b in zip(gp1, gp2):
+            assert (a is None) == (b is None)
+            if a is not None:
+                assert torch.equal(a, b)
+        n_f = sum(g is not None for (n, _), g in zip(m.named_parameters(), gp1) if n.startswith("rwkv_wrapper_forward"))
+        n_b = sum(g is not None for (n, _), g in zip(m.named_parameters(), gp1) if n.startswith("rwkv_wrapper_backward"))
+        outcomes.add((n_f > 0, n_b > 0))
+    assert outcomes == {(True, True), (True, False), (False, True)} and len(slot._graphs) == 3
