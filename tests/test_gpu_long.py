@@ -381,3 +381,30 @@ def test_time_segmented_backward_is_faster():
     t_seg = ms()
     print(f"\nbackward B=1 T=12499 H=8 both directions: one CTA per sequence {t_plain:.3f} ms, time-segmented {t_seg:.3f} ms")
     assert t_seg < 0.5 * t_plain
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_one_process_two_devices():
+    """One host process driving two GPUs (DataParallel-style, a server looping over devices): the dynamic-shared-memory opt-in
+    is a per-device function attribute and the tensor-map cache is keyed by pointer, so every kernel must work on cuda:1
+    after cuda:0 (a process-wide `static bool` had opted in on the first device only)."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import ops
+    from paper_accurate_fast_cheap_b200.convolution import convmod_core
+    inp = _inputs(2, 300, 4, torch.bfloat16, seed=71)
+    ref_y, _ = oracle.fwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], prec="f64")
+    ref_g = oracle.bwd(inp["r"], inp["k"], inp["v"], inp["w"], inp["u"], inp["gy"], prec="f64")
+    for dev in ("cuda:0", "cuda:1", "cuda:0"):
+        g = {n: t.to(dev).contiguous() for n, t in inp.items()}
+        f = tuple(g[n] for n in "rkvwu")
+        ck = ops.checkpoint_buffer(g["r"], 2)
+        y_f, y_b, _, _ = pk.bi_forward_raw(f, f, ckpt=ck)
+        of, _ = pk.bi_backward_raw(f, f, g["gy"], g["gy"], ckpt=ck)
+        assert y_f.device == torch.device(dev)
+        assert oracle.rel_err(y_f, ref_y) <= TOL[torch.bfloat16]
+        assert oracle.rel_err(of[3], ref_g[3]) <= TOL[torch.bfloat16]
+        y32, _ = pk.wkv6_forward_raw(*(t.float() for t in f))                     # exact scan kernels
+        assert oracle.rel_err(y32, ref_y) <= 1e-5
+        z = torch.randn(2, 100, 512, device=dev)
+        out = convmod_core(z, torch.randn(256, 31, device=dev), None, torch.ones(256, device=dev), torch.zeros(256, device=dev), 1e-5, 100, 15)
+        assert out.device == torch.device(dev) and bool(torch.isfinite(out).all())
