@@ -58,16 +58,22 @@ struct LeanSmem {
 // The CTA processes the chunks [cbeg, cbeg + nchunks) of its sequence (processing order), starting from the state *s0p
 // (null: zero) and leaving the final state in *sTp (unless null); decay_out (unless null) receives the product of all
 // per-step decays of that range per key channel.  Unsegmented: cbeg = 0, nchunks = all.
-// kStateOnly: pass 1 of the time-segmented forward (no outputs, no checkpoints, S_0 = 0, decay product out) -- a
-// compile-time mode, so that the normal instantiation carries none of its code (and vice versa).
-template <bool kStateOnly>
+// kMode is compile-time, so that the normal instantiation carries none of the other modes' code (and vice versa):
+//   kNormal     the whole range from *s0p, outputs (and checkpoints)
+//   kStateOnly  pass 1 of the two-pass time-segmented forward: no outputs, no checkpoints, S_0 = 0, decay product out
+//   kLocalOut   the one-pass time-segmented forward: outputs computed from S_0 = 0 (wkv6_fwd_corr_kernel adds the carried
+//               state's share afterwards), local end state and decay product out, and per chunk the decay product from the
+//               start of the segment to the start of the chunk (prefix_out[chunk][64])
+constexpr int kNormal = 0, kStateOnly = 1, kLocalOut = 2;
+template <int kMode>
 __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const DirArgs& D, const int b, const int h, const int bh,
                                           const bool REV, const int cbeg, const int nchunks, const float* s0p_, float* sTp,
-                                          float* decay_out_, const bool skip_y_, const bool ckpt_on_) {
-    const float* const s0p = kStateOnly ? nullptr : s0p_;
-    float* const decay_out = kStateOnly ? decay_out_ : nullptr;
-    const bool skip_y = kStateOnly ? true : skip_y_;
-    const bool ckpt_on = kStateOnly ? false : ckpt_on_;
+                                          float* decay_out_, const bool skip_y_, const bool ckpt_on_, float* prefix_out_ = nullptr) {
+    const float* const s0p = kMode == kNormal ? s0p_ : nullptr;
+    float* const decay_out = kMode == kNormal ? nullptr : decay_out_;
+    const bool skip_y = kMode == kStateOnly ? true : kMode == kLocalOut ? false : skip_y_;
+    const bool ckpt_on = kMode == kNormal ? ckpt_on_ : false;
+    float* const prefix_out = kMode == kLocalOut ? prefix_out_ : nullptr;
     const int tid = threadIdx.x, lane = tid & 31;
     const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);
     // warp index through a lane-0 broadcast: the compiler then keeps it (and everything derived from it: MMA operands,
@@ -426,6 +432,10 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             const float* bt = &sm.blocktot[par][0][0];
             const float f0 = ex2(-((bt[frow] + bt[N + frow]) + (bt[2 * N + frow] + bt[3 * N + frow])));
             const float f1 = ex2(-((bt[frow + 8] + bt[N + frow + 8]) + (bt[2 * N + frow + 8] + bt[3 * N + frow + 8])));
+            if (kMode == kLocalOut && half == 0 && (lane & 3) == 0) {   // decay from the start of the segment to the start of chunk c
+                prefix_out[c * N + frow] = dprod0;
+                prefix_out[c * N + frow + 8] = dprod1;
+            }
             dprod0 *= f0;
             dprod1 *= f1;
 #pragma unroll
@@ -497,7 +507,12 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
 #undef TMA_THR
 }
 
-__global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __grid_constant__ Params p) {
+// Two kernels share this top level: wkv6_fwd_chunk_lean_kernel carries ONLY the normal body (whole sequences, and pass 2 of
+// the two-pass segmented scheme), wkv6_fwd_chunk_seg_kernel the two segment-local bodies (state-only pass 1; local outputs of
+// the one-pass scheme).  With all three bodies in one kernel (9 500 SASS instructions) the normal launch was 0.9 us slower
+// (41.2 vs 40.3 us) -- instruction-cache footprint of code it never runs.
+template <bool kSegKernel>
+__device__ __forceinline__ void lean_top(const Params& p) {
     extern __shared__ __align__(1024) uint8_t smem_bytes[];
     // offset arithmetic on the __shared__ array (not a uintptr_t round trip) keeps the address space visible to the
     // compiler: LDS/STS instead of generic LD/ST
@@ -524,23 +539,31 @@ __global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __gri
     // Unsegmented: the whole sequence from S_0 to S_T.  Time-segmented: pass 1 (seg_mode 1) leaves every
     // segment's local state (from S = 0) and decay product in the scratch, a small scan kernel turns them into the
     // segment-start states, pass 2 (seg_mode 2) recomputes every segment from its start state.
-    const bool segd = p.nseg > 1, pass1 = segd && p.seg_mode == 1;
+    const bool segd = p.nseg > 1, pass1 = segd && p.seg_mode != 2;      // seg_mode 1: state-only pass 1; 3: local outputs
     const int cbeg = segd ? seg * p.seg_chunks : 0;
     const int nloc = segd ? min(p.seg_chunks, ntot - cbeg) : ntot;
     float* const slot = segd ? p.seg_state + ((size_t)seq * nseg + seg) * N * N : nullptr;
     const float* const s0p = pass1 ? nullptr : segd ? slot : (D.s0 ? D.s0 + (size_t)bh * N * N : nullptr);
     float* const sTp = pass1 ? slot : ((!segd || seg == nseg - 1) && D.sT) ? D.sT + (size_t)bh * N * N : nullptr;
     float* const dec = pass1 ? p.seg_decay + ((size_t)seq * nseg + seg) * N : nullptr;
-    if (pass1)
-        lean_body<true>(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, nullptr, sTp, dec, true, false);
-    else
-        lean_body<false>(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, s0p, sTp, nullptr, p.skip_y != 0, D.ckpt != nullptr);
+    if (kSegKernel) {
+        if (p.seg_mode == 3)
+            lean_body<kLocalOut>(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, nullptr, sTp, dec, false, false,
+                                 p.seg_prefix + ((size_t)seq * ntot + cbeg) * N);
+        else
+            lean_body<kStateOnly>(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, nullptr, sTp, dec, true, false);
+    } else {
+        lean_body<kNormal>(p, sm, D, b, h, bh, D.reverse != 0, cbeg, nloc, s0p, sTp, nullptr, p.skip_y != 0, D.ckpt != nullptr);
+    }
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 1024) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.dbg[130 + 4 * blockIdx.x] = t;
     }
 }
+
+__global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_lean_kernel(const __grid_constant__ Params p) { lean_top<false>(p); }
+__global__ void __launch_bounds__(256, 2) wkv6_fwd_chunk_seg_kernel(const __grid_constant__ Params p) { lean_top<true>(p); }
 
 // Segment scan: S_start[0] = S_0 (or 0), S_start[s+1][i][j] = S_start[s][i][j] * D_s[j] + dS_s[i][j]; the slots that pass 1
 // filled with dS_s are overwritten with S_start[s].  One thread per state element, grid = sequences x 16: every thread
@@ -568,6 +591,179 @@ __global__ void __launch_bounds__(256) wkv6_seg_scan_kernel(const __grid_constan
             st[(size_t)s * N * N] = cur;
             cur = fmaf(cur, dk[s], dS[s]);
         }
+    if (p.seg_mode == 3 && D.sT) D.sT[(size_t)bh * N * N + e] = cur;   // one-pass scheme: nobody else computes S_T
+}
+
+// One-pass time-segmented forward, second kernel: y of every chunk outside the first segment was computed from S = 0 at the
+// start of its segment; the state carried into the segment contributes  y_p += sum_j r_p[j] 2^(A_p[j]) Dp[j] S_start[.][j],
+// Dp = decay from the start of the segment to the start of the chunk (written per chunk by the first kernel), S_start from
+// the segment scan.  One CTA per (sequence, chunk), no dependence between CTAs: r, w and y tiles by TMA, the r 2^(A_p) Dp tile
+// rebuilt from r and w (decays, in-block cumulative sums -- the R side of the main kernel's tile building), one M64 N64 K64
+// MMA group against the bf16 copy of S_start, y tile updated in shared memory and stored back.  41 KB, 64 TMEM columns.
+struct CorrSmem {
+    alignas(1024) uint8_t raw_r[CL * 128];
+    alignas(1024) uint8_t raw_w[CL * 128];
+    alignas(1024) uint8_t y[CL * 128];
+    alignas(1024) uint8_t rc[CL * 128];      // r 2^(A_p) Dp, K-major [p][j]
+    alignas(1024) uint8_t sp[N * 128];       // S_start^T [j][i] bf16 (MN-major B operand, as in the main kernel)
+    float blocktot[4][N];
+    alignas(8) uint64_t bar_in, bar_m;
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(256) wkv6_fwd_corr_kernel(const __grid_constant__ Params p) {
+    extern __shared__ __align__(1024) uint8_t smem_bytes[];
+    CorrSmem& sm = *reinterpret_cast<CorrSmem*>(smem_bytes + ((1024u - (smem_u32(smem_bytes) & 1023u)) & 1023u));
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    // corr_first: the first chunk that needs the correction -- seg_chunks (the first segment starts from S_0 = 0 and is
+    // already right) or 0 (a caller-supplied S_0 is carried into the first segment like any other start state)
+    const int BH = p.B * p.H, ntot = (p.T + CL - 1) / CL, per_seq = ntot - p.corr_first;
+    const int seq = blockIdx.x / per_seq, c = p.corr_first + (blockIdx.x - seq * per_seq);   // chunk in processing order
+    const int seg = c / p.seg_chunks;
+    const int ds = seq / BH, bh = seq - ds * BH, b = bh / p.H, h = bh - b * p.H;
+    const DirArgs& D = p.d[ds];
+    const bool rev = D.reverse != 0;
+    const int q = rev ? ntot - 1 - c : c, t0 = q * CL;
+    if (tid == 0) {
+        mbar_init(&sm.bar_in, 1);
+        mbar_init(&sm.bar_m, 1);
+        fence_barrier_init();
+        fence_proxy_async();
+        mbar_arrive_expect_tx(&sm.bar_in, 3u * CL * 128);
+        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_in, h * N, t0, b);
+        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_in, h * N, t0, b);
+        tma_load_3d(sm.y, &D.my, &sm.bar_in, h * N, t0, b);
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // S_start [i][j] fp32 -> bf16 tile [j][i] (16 elements per thread: i = tid >> 2, j = 16 * (tid & 3) ..)
+    {
+        const float* S = p.seg_state + ((size_t)seq * p.nseg + seg) * N * N;
+        const int i = tid >> 2, j0 = 16 * (tid & 3);
+#pragma unroll
+        for (int v4 = 0; v4 < 4; v4++) {
+            const float4 f = *reinterpret_cast<const float4*>(S + i * N + j0 + 4 * v4);
+            const float vals[4] = {f.x, f.y, f.z, f.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int j = j0 + 4 * v4 + e;
+                *reinterpret_cast<__nv_bfloat16*>(sm.sp + sw_chunk(j, i >> 3) + (i & 7) * 2) = __float2bfloat16_rn(vals[e]);
+            }
+        }
+    }
+    const int qtr = warp & 3, half = warp >> 2;
+    const int frow = 16 * qtr + (lane >> 2);
+    const int fcol = 32 * half + 2 * (lane & 3);
+    const uint32_t lane_field = (uint32_t)(qtr * 32) << 16;
+    const int I = warp & 3, ch = warp >> 2;
+    const int cq = lane & 7, rg = lane >> 3;
+    const int c0 = 32 * ch + 4 * cq;
+    const int coff = (c0 & 7) * 2, cchunk = c0 >> 3;
+    float pre[4];
+    {
+        const float4 f = *reinterpret_cast<const float4*>(p.seg_prefix + ((size_t)seq * ntot + c) * N + c0);
+        pre[0] = f.x; pre[1] = f.y; pre[2] = f.z; pre[3] = f.w;
+    }
+    __syncthreads();   // the barriers thread 0 initialised are visible before anybody waits on them
+    mbar_wait(&sm.bar_in, 0);
+    float ro[4][4];
+    {
+        float l2[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int pos = 16 * I + 4 * rg + r;
+            const int row = rev ? 63 - pos : pos;
+            const int off = sw_chunk(row, cchunk) + coff;
+            float w4[4];
+            ld4bf(sm.raw_r + off, ro[r]);
+            ld4bf(sm.raw_w + off, w4);
+            const bool valid = t0 + row < p.T;
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float x = ex2(w4[e] * kLog2e);
+                l2[r][e] = valid ? fmaxf(-x * kLog2e, -kClampL2) : 0.f;
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            l2[1][e] += l2[0][e];
+            l2[2][e] += l2[1][e];
+            l2[3][e] += l2[2][e];
+        }
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            float x = l2[3][e];
+            float y = __shfl_up_sync(0xffffffffu, x, 8);
+            if (rg >= 1) x += y;
+            y = __shfl_up_sync(0xffffffffu, x, 16);
+            if (rg >= 2) x += y;
+            const float excl = x - l2[3][e];
+            if (rg == 3) sm.blocktot[I][c0 + e] = x;
+#pragma unroll
+            for (int r = 0; r < 4; r++) ro[r][e] *= ex2(excl + (r ? l2[r - 1][e] : 0.f));
+        }
+    }
+    __syncthreads();   // blocktot visible; tmem_base visible
+    {
+        float fst[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            float s_ = 0.f;
+#pragma unroll
+            for (int m = 0; m < 4; m++)
+                if (m < I) s_ += sm.blocktot[m][c0 + e];
+            fst[e] = ex2(s_) * pre[e];
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int pos = 16 * I + 4 * rg + r;
+            const int row = rev ? 63 - pos : pos;
+            float x4[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) x4[e] = ro[r][e] * fst[e];
+            st4bf(sm.rc + sw_chunk(row, cchunk) + coff, x4);
+        }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tY = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
+    if (warp == 0 && elect_one()) {
+        const uint64_t dk_rc = desc_k(smem_u32(sm.rc)), dm_sp = desc_mn(smem_u32(sm.sp));
+        constexpr uint32_t ID = umma_idesc(0, 1, 64, 64);
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++) umma(tY, dk_rc + (uint64_t)((ks * 32) >> 4), dm_sp + (uint64_t)((ks * 2048) >> 4), ID, ks > 0);
+        umma_commit(&sm.bar_m);
+    }
+    __syncwarp();
+    mbar_wait(&sm.bar_m, 0);
+    tc_fence_after();
+    {
+        float x[16];
+        tmem_ld_16x32(tY + lane_field + 32 * half, x);
+#pragma unroll
+        for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++) {
+                const int col = fcol + 8 * rep;
+                uint32_t* wp = reinterpret_cast<uint32_t*>(sm.y + sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2);
+                const uint32_t old = *wp;
+                *wp = pack_bf16(__uint_as_float(old << 16) + x[4 * rep + 2 * hh], __uint_as_float(old & 0xffff0000u) + x[4 * rep + 2 * hh + 1]);
+            }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+        tma_store_3d(&D.my, sm.y, h * N, t0, b);
+        tma_store_commit();
+        tma_store_wait<0>();
+    }
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tY) : "memory");
 }
 
 // Number of time segments for a launch (0 = unsegmented): only when one CTA per sequence leaves SM slots empty and the
@@ -583,7 +779,7 @@ static int pick_segments(const Params& p, size_t scratch_bytes, int min_seg, int
     if (nseg < min_seg) return 0;
     int sc = (ntot + nseg - 1) / nseg;
     nseg = (ntot + sc - 1) / sc;                 // no empty segments
-    const size_t need = (size_t)nseq * nseg * (N * N + N) * sizeof(float);
+    const size_t need = (size_t)nseq * (nseg * (N * N + N) + (size_t)ntot * N) * sizeof(float);   // + per-chunk decay prefixes
     if (need > scratch_bytes) return 0;
     *seg_chunks = sc;
     return nseg;
@@ -599,6 +795,7 @@ bool plan_segments(Params& q, void* scratch, size_t scratch_bytes, int min_seg) 
     q.seg_chunks = sc;
     q.seg_state = static_cast<float*>(scratch);
     q.seg_decay = q.seg_state + (size_t)nseq * nseg * N * N;
+    q.seg_prefix = q.seg_decay + (size_t)nseq * nseg * N;
     return true;
 }
 
@@ -606,7 +803,7 @@ bool plan_segments(Params& q, void* scratch, size_t scratch_bytes, int min_seg) 
 size_t segment_scratch_bytes(const Params& p, int min_seg) {
     int sc = 0;
     const int nseg = pick_segments(p, ~(size_t)0, min_seg, &sc);
-    return nseg ? (size_t)p.ndir * p.B * p.H * nseg * (N * N + N) * sizeof(float) : 0;
+    return nseg ? (size_t)p.ndir * p.B * p.H * (nseg * (N * N + N) + (size_t)((p.T + CL - 1) / CL) * N) * sizeof(float) : 0;
 }
 
 int launch_seg_scan(const Params& q, cudaStream_t st) {
@@ -620,6 +817,35 @@ int launch_seg_scan(const Params& q, cudaStream_t st) {
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
     Params q = p;
     if (!plan_segments(q, scratch, scratch_bytes, 2)) return -1;
+    bool any_ckpt = q.skip_y != 0;
+    for (int d = 0; d < q.ndir; d++) any_ckpt = any_ckpt || q.d[d].ckpt != nullptr;
+    if (!any_ckpt) {
+        // inference: ONE pass over the inputs -- outputs from the zero-start state of every segment, the segment scan, then
+        // the carried state's share added to y (wkv6_fwd_corr_kernel) -- instead of a state-only pass plus a full pass
+        q.seg_mode = 3;
+        int e = launch_fwd_chunk(q, st);
+        if (e) return e;
+        if ((e = launch_seg_scan(q, st))) return e;
+        const size_t smem = sizeof(CorrSmem) + 1024;
+        static std::atomic<unsigned long long> opted{0};
+        int dev = 0;
+        cudaError_t ce = cudaGetDevice(&dev);
+        if (ce != cudaSuccess) return (int)ce;
+        if (!(opted.load(std::memory_order_acquire) & (1ull << (dev & 63)))) {
+            if ((ce = cudaFuncSetAttribute(wkv6_fwd_corr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return (int)ce;
+            cudaFuncSetAttribute(wkv6_fwd_corr_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+            opted.fetch_or(1ull << (dev & 63), std::memory_order_release);
+        }
+        const int ntot = (q.T + CL - 1) / CL;
+        Params qc = q;
+        qc.dbg = nullptr;
+        qc.corr_first = q.seg_chunks;
+        for (int d = 0; d < q.ndir; d++)
+            if (q.d[d].s0) qc.corr_first = 0;
+        wkv6_fwd_corr_kernel<<<dim3(q.ndir * q.B * q.H * (ntot - qc.corr_first)), dim3(256), smem, st>>>(qc);
+        count_launch(1);
+        return (int)cudaGetLastError();
+    }
     q.seg_mode = 1;
     int e = launch_fwd_chunk(q, st);
     if (e) return e;
@@ -630,11 +856,14 @@ int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_by
 
 int launch_fwd_chunk(const Params& p, cudaStream_t st) {
     const size_t smem = sizeof(LeanSmem) + 1024;
-    cudaError_t e = opt_in_smem_once(wkv6_fwd_chunk_lean_kernel, smem, 0);
+    const bool seg_local = p.nseg > 1 && p.seg_mode != 2;          // pass 1 of either segmented scheme
+    cudaError_t e = seg_local ? opt_in_smem_once(wkv6_fwd_chunk_seg_kernel, smem, 2) : opt_in_smem_once(wkv6_fwd_chunk_lean_kernel, smem, 0);
     if (e != cudaSuccess) return (int)e;
     Params q = p;
     q.dbg = debug_trace_buffer();
-    e = launch_pdl(wkv6_fwd_chunk_lean_kernel, dim3(q.ndir * q.B * q.H * (q.nseg > 0 ? q.nseg : 1)), dim3(256), smem, st, q);
+    const dim3 grid(q.ndir * q.B * q.H * (q.nseg > 0 ? q.nseg : 1));
+    e = seg_local ? launch_pdl(wkv6_fwd_chunk_seg_kernel, grid, dim3(256), smem, st, q)
+                  : launch_pdl(wkv6_fwd_chunk_lean_kernel, grid, dim3(256), smem, st, q);
     count_launch(1);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }

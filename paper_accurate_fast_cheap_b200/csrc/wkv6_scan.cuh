@@ -41,6 +41,8 @@ struct Params {
     float* seg_state;                     // [ndir][B*H][nseg][64 i][64 j]: pass 1 writes dS, the scan turns it into S_start
     float* seg_decay;                     // [ndir][B*H][nseg][64 j]: product of the per-step decays of the segment
     float* seg_gu;                        // time-segmented backward: [ndir][B*H][nseg][64] partial gu of every segment
+    int corr_first;                       // one-pass segmented forward: first chunk wkv6_fwd_corr_kernel touches
+    float* seg_prefix;                    // one-pass segmented forward: [ndir][B*H][chunks][64] decay from segment start to chunk start
     unsigned long long* dbg;              // optional clock64() trace of one CTA (wkv6_b200_debug_trace), else null
 };
 

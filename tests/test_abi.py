@@ -51,8 +51,9 @@ def test_argument_validation_without_gpu(built):
     # time segmentation: only few, long sequences; the size is what the planner will use (<= 40 segments per sequence)
     assert L.wkv6_b200_forward_scratch_bytes(0, 16, 750, 512, 8, 2) == 0            # short
     assert L.wkv6_b200_forward_scratch_bytes(0, 16, 30000, 512, 8, 2) == 0          # 256 sequences: SMs are full
-    assert L.wkv6_b200_forward_scratch_bytes(0, 1, 30000, 512, 8, 2) == 16 * 18 * (64 * 64 + 64) * 4
-    assert L.wkv6_b200_forward_scratch_bytes(0, 1, 40000, 256, 4, 1) == 4 * 40 * (64 * 64 + 64) * 4
+    # per sequence: nseg x (state + decay product) + chunks x decay prefix (the one-pass scheme's correction kernel)
+    assert L.wkv6_b200_forward_scratch_bytes(0, 1, 30000, 512, 8, 2) == 16 * (18 * (64 * 64 + 64) + 469 * 64) * 4
+    assert L.wkv6_b200_forward_scratch_bytes(0, 1, 40000, 256, 4, 1) == 4 * (40 * (64 * 64 + 64) + 625 * 64) * 4
     assert L.wkv6_b200_forward_scratch_bytes(1, 1, 90000, 1024, 16, 2) > 0
 
 
