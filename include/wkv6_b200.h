@@ -97,6 +97,22 @@ int wkv6_b200_forward(int dtype, int B, int T, int C, int H,
                       const float* s0, void* y, float* sT, void* ckpt, int reverse,
                       void* scratch, size_t scratch_bytes, void* stream);
 
+/* wkv6_b200_forward for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc): the same kernels on the same arguments, with the time-segmentation scratch taken
+ * from a fixed array inside the library (a file-scope `static __device__` array of WKV6_STATIC_SCRATCH_BYTES, which
+ * every GPU that loads the library holds until exit) instead of a caller-owned buffer.  The call allocates and frees
+ * nothing.  A shape whose wkv6_b200_forward_scratch_bytes() exceeds WKV6_STATIC_SCRATCH_BYTES is rejected with
+ * WKV6_E_BADARG (wkv6_b200_last_error() names both sizes); a shape that would not be segmented runs one CTA per sequence
+ * and does not touch the array.  Nothing in the array has to start at zero (every element a launch reads was written
+ * earlier in the same call), so it is not cleared, and it keeps the last call's contents.  ALL calls on a device share
+ * the one array: calls that can overlap on the GPU (different streams without an ordering between them, or different
+ * host threads) race on it -- keep them on one stream or order them with events.
+ * No counterpart in the reference. */
+#define WKV6_STATIC_SCRATCH_BYTES (16u << 20)
+int wkv6_b200_forward_static_scratch(int dtype, int B, int T, int C, int H,
+                                     const void* r, const void* k, const void* v, const void* w, const void* u,
+                                     const float* s0, void* y, float* sT, void* ckpt, int reverse, void* stream);
+
 /* Bytes of workspace the backward entry points need when they are given no checkpoints (0 is possible). */
 size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H, int ndirections);
 /* Time segmentation of the bf16 backward (optional), the counterpart of the forward's: with few, long sequences

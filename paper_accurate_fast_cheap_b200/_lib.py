@@ -15,7 +15,7 @@ ALGO_AUTO, ALGO_SCAN, ALGO_CHUNK = 0, 1, 2
 # every symbol include/wkv6_b200.h declares
 SYMBOLS = (
     "wkv6_b200_abi_version", "wkv6_b200_last_error", "wkv6_b200_launch_count", "wkv6_b200_set_algo",
-    "wkv6_b200_get_algo", "wkv6_b200_debug_trace", "wkv6_b200_forward_scratch_bytes", "wkv6_b200_debug_trace_ctas", "wkv6_b200_checkpoint_bytes", "wkv6_b200_forward", "wkv6_b200_backward_workspace_bytes", "wkv6_b200_backward_scratch_bytes", "wkv6_b200_backward",
+    "wkv6_b200_get_algo", "wkv6_b200_debug_trace", "wkv6_b200_forward_scratch_bytes", "wkv6_b200_debug_trace_ctas", "wkv6_b200_checkpoint_bytes", "wkv6_b200_forward", "wkv6_b200_forward_static_scratch", "wkv6_b200_backward_workspace_bytes", "wkv6_b200_backward_scratch_bytes", "wkv6_b200_backward",
     "wkv6_b200_bi_forward", "wkv6_b200_bi_backward", "wkv6_b200_combine", "wkv6_b200_tmix_mix", "wkv6_b200_tmix_mix_backward", "wkv6_b200_ln_pair_cat", "wkv6_b200_convmod_core",
 )
 
@@ -51,6 +51,8 @@ def lib() -> ctypes.CDLL:
     L.wkv6_b200_checkpoint_bytes.restype = _sz
     L.wkv6_b200_forward.argtypes = [_i] * 5 + [_vp] * 9 + [_i, _vp, _sz, _vp]
     L.wkv6_b200_forward.restype = _i
+    L.wkv6_b200_forward_static_scratch.argtypes = [_i] * 5 + [_vp] * 9 + [_i, _vp]
+    L.wkv6_b200_forward_static_scratch.restype = _i
     L.wkv6_b200_backward_workspace_bytes.argtypes = [_i] * 6
     L.wkv6_b200_backward_workspace_bytes.restype = _sz
     L.wkv6_b200_backward_scratch_bytes.argtypes = [_i] * 6

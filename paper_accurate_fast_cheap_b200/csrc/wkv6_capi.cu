@@ -78,10 +78,10 @@ static unsigned map_hash(const MapKey& k) {
     return (unsigned)(h >> 40) & (kMapSlots - 1);
 }
 
+static thread_local bool ctx_bound = false;
 static void bind_context_once() {
     // cuTensorMapEncodeTiled wants a current context; threads that never touched the runtime (autograd workers)
     // have none until a runtime call binds the primary context.
-    static thread_local bool ctx_bound = false;
     if (!ctx_bound) { cudaFree(nullptr); ctx_bound = true; }
 }
 
@@ -186,6 +186,37 @@ static int fill_fwd(DirArgs& d, int dtype, int B, int T, int C, const FwdSet& s,
     }
     d.u = s.u; d.s0 = s.s0; d.sT = s.sT; d.y = s.y;
     d.reverse = reverse;
+    return 0;
+}
+
+// ---- wkv6_b200_forward_static_scratch: the segmentation scratch of callers that must not allocate.
+// One array per device that loads this library, held until exit.  `g_static_scratch` in HOST code is only a handle of the
+// symbol (its host-side shadow), never a device address: the device address comes from cudaGetSymbolAddress, looked up once
+// per device with that device current, and is what the kernels are given.
+static __device__ __align__(256) unsigned char g_static_scratch[WKV6_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+static std::atomic<void*> g_static_scratch_ptr[kMaxDevices];    // zero-initialised
+
+static int static_scratch_address(void** out) {
+    int dev = 0;
+    cudaError_t ce = cudaGetDevice(&dev);
+    if (ce != cudaSuccess) return cuda_fail((int)ce, "forward_static_scratch: cudaGetDevice");
+    if (dev < 0 || dev >= kMaxDevices) return fail(WKV6_E_BADARG, "forward_static_scratch: device ordinal %d (at most %d)", dev, kMaxDevices);
+    if (!ctx_bound) {
+        // a thread that never touched the runtime has no current context for cuTensorMapEncodeTiled: cudaSetDevice binds the
+        // primary context (and, unlike bind_context_once, is not spelled cudaFree)
+        if ((ce = cudaSetDevice(dev)) != cudaSuccess) return cuda_fail((int)ce, "forward_static_scratch: cudaSetDevice");
+        ctx_bound = true;
+    }
+    void* ptr = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+    if (!ptr) {
+        ce = cudaGetSymbolAddress(&ptr, g_static_scratch);     // the current device's copy of the array
+        if (ce != cudaSuccess) return cuda_fail((int)ce, "forward_static_scratch: cudaGetSymbolAddress");
+        if (!ptr || !aligned16(ptr)) return fail(WKV6_E_BADARG, "forward_static_scratch: bad symbol address");
+        g_static_scratch_ptr[dev].store(ptr, std::memory_order_release);   // racing threads store the same value
+    }
+    *out = ptr;
     return 0;
 }
 
@@ -377,6 +408,25 @@ int wkv6_b200_forward(int dtype, int B, int T, int C, int H, const void* r, cons
     const FwdSet s = {r, k, v, w, u, s0, y, sT, ckpt};
     const int rv = reverse != 0;
     return run_forward(dtype, B, T, C, H, &s, &rv, 1, scratch, scratch_bytes, stream);
+}
+
+int wkv6_b200_forward_static_scratch(int dtype, int B, int T, int C, int H, const void* r, const void* k, const void* v,
+                                     const void* w, const void* u, const float* s0, void* y, float* sT, void* ckpt,
+                                     int reverse, void* stream) {
+    int e = check_common(dtype, B, T, C, H);
+    if (e) return e;
+    const size_t need = wkv6_b200_forward_scratch_bytes(dtype, B, T, C, H, 1);
+    if (need > (size_t)WKV6_STATIC_SCRATCH_BYTES)
+        return fail(WKV6_E_BADARG, "forward_static_scratch: this shape segments on %zu bytes of scratch, the static array holds "
+                    "%zu (WKV6_STATIC_SCRATCH_BYTES): use wkv6_b200_forward with a caller-owned buffer", need,
+                    (size_t)WKV6_STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    if (need && B > 0) {
+        if ((e = static_scratch_address(&scratch))) return e;
+    }
+    const FwdSet s = {r, k, v, w, u, s0, y, sT, ckpt};
+    const int rv = reverse != 0;
+    return run_forward(dtype, B, T, C, H, &s, &rv, 1, scratch, scratch ? (size_t)WKV6_STATIC_SCRATCH_BYTES : 0, stream);
 }
 
 size_t wkv6_b200_backward_scratch_bytes(int dtype, int B, int T, int C, int H, int ndirections) {
