@@ -286,11 +286,11 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         // ================= phase 1: decays, in-block cumulative sums, Rtil, Ktil(own), bonus
         mbar_wait(&sm.bar_rkw, par);
         WKV6_TS(64, 1);
-        float eo[4][4], ei[4][4], ew[4][4], bt[4];
+        float eo[4][4], ei[4][4], ew[4][4], ebt[4];           // ebt = 2^(log2 decay total of the own sub-block)
         uint2 rpk[4], kpk[4];                            // this thread's r and k (bf16 x4 per row) for the later phases
         int rows[4];
         {
-            float rr[4][4], kk[4][4], l2[4][4], bsum[4];
+            float rr[4][4], kk[4][4], l2[4][4], dstep[4][4], bsum[4];
             float xmax = 0.f;
 #pragma unroll
             for (int r = 0; r < 4; r++) {
@@ -314,6 +314,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     xmax = fmaxf(xmax, x);
                     const float l = fmaxf(-x * kLog2e, -kClampL2);
                     l2[r][e] = valid ? l : 0.f;
+                    dstep[r][e] = ex2(l2[r][e]);                    // the step's decay
                 }
                 bsum[r] = bs;
             }
@@ -346,15 +347,25 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 excl[e] = x - l2[3][e];
                 if (rg == 3) sm.blocktot[I][c0 + e] = x;
             }
+            // eo[r] = 2^(A_p - a_I), ei[r] = 2^-(A+_p - a_I) of the thread's four consecutive steps: one ex2 at each end of the run
+            // and products of the step decays in between (the MUFU pipe, 16 lanes per clock per SM, bounds this phase: 6 ex2
+            // per channel instead of 8)
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                eo[0][e] = ex2(excl[e]);
+                eo[1][e] = eo[0][e] * dstep[0][e];
+                eo[2][e] = eo[1][e] * dstep[1][e];
+                eo[3][e] = eo[2][e] * dstep[2][e];
+                ei[3][e] = ex2(-(excl[e] + l2[3][e]));
+                ei[2][e] = ei[3][e] * dstep[3][e];
+                ei[1][e] = ei[2][e] * dstep[2][e];
+                ei[0][e] = ei[1][e] * dstep[1][e];
+            }
 #pragma unroll
             for (int r = 0; r < 4; r++) {
                 float ro[4], ko[4];
 #pragma unroll
                 for (int e = 0; e < 4; e++) {
-                    const float aex = excl[e] + (r ? l2[r - 1][e] : 0.f);   // A_p  - a_I   (<= 0)
-                    const float ain = excl[e] + l2[r][e];                   // A+_p - a_I   (<= 0)
-                    eo[r][e] = ex2(aex);
-                    ei[r][e] = ex2(-ain);
                     ro[e] = rr[r][e] * eo[r][e];
                     ko[e] = kk[r][e] * ei[r][e];
                 }
@@ -373,58 +384,71 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 
         // ================= phase 1b: cross-block factors -> Rst, Ktil(I' > I), Kend, Rtil'(J <= I)
         {
-            float tot[4][4];   // blocktot[m][c0 + e]
+            // Six factors per channel: fst = 2^(a_I);  fk[m] = 2^(a_{m+1} - a_I), m >= I (m = 3: chunk end);  fr[J] = 2^(a_I - a_{J+1}),
+            // J <= I.  The four row groups of a warp work on the same channels: lane (rg, cq) computes the six of channel c0 + rg and
+            // the warp exchanges them through 768 bytes of the gw staging tile (idle until the final epilogue; its TMA store
+            // was waited for at the top of the chunk): 6 ex2 per lane instead of 36 -- the MUFU pipe bounds this phase.
+            // Slots [6][32 channels]: m < I: fr[m];  m >= I: fk[m];  4: fr[I];  5: fst.
+            float* const fac = reinterpret_cast<float*>(sm.o_gw) + warp * 192;
+            {
+                float tot[4];
 #pragma unroll
-            for (int m = 0; m < 4; m++) {
-                const float4 t = *reinterpret_cast<const float4*>(&sm.blocktot[m][c0]);
-                tot[m][0] = t.x; tot[m][1] = t.y; tot[m][2] = t.z; tot[m][3] = t.w;
-            }
-            float fst[4], fk[4][4], fr[4][4];   // 2^(a_I);  fk[I'] = 2^(a_I' - a_I) (I' = 4: chunk end);  fr[J] = 2^(a_I - a_{J+1})
+                for (int m = 0; m < 4; m++) tot[m] = sm.blocktot[m][c0 + rg];
+                float pre = 0.f, totI = tot[0];
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
-                float s = 0.f;
-#pragma unroll
-                for (int m = 0; m < 4; m++)
-                    if (m < I) s += tot[m][e];
-                fst[e] = ex2(s);
-                bt[e] = tot[0][e];
-#pragma unroll
-                for (int m = 1; m < 4; m++)
-                    if (m == I) bt[e] = tot[m][e];
+                for (int m = 0; m < 4; m++) {
+                    if (m < I) pre += tot[m];
+                    if (m == I) totI = tot[m];
+                }
+                float* const f = fac + 4 * cq + rg;
+                f[5 * 32] = ex2(pre);
+                f[4 * 32] = ex2(-totI);
                 float acc = 0.f;
 #pragma unroll
-                for (int m = 0; m < 4; m++) {       // fk[m] for target I' = m + 1
-                    if (m >= I) acc += tot[m][e];
-                    fk[m][e] = ex2(acc);
-                }
-                // fr[J], J <= I: exponent a_I - a_{J+1} = -bt (J = I), 0 (J = I-1), sum_{m=J+1}^{I-1} tot[m] otherwise
+                for (int m = 0; m < 4; m++)
+                    if (m >= I) {               // target variant I' = m + 1
+                        acc += tot[m];
+                        f[m * 32] = ex2(acc);
+                    }
+                // fr[J], J < I: exponent a_I - a_{J+1} = 0 (J = I-1), sum_{m=J+1}^{I-1} tot[m] otherwise
                 float acr = 0.f;
 #pragma unroll
-                for (int J = 3; J >= 0; J--) {
-                    if (J == I) fr[J][e] = ex2(-bt[e]);
-                    else if (J < I) {
-                        fr[J][e] = ex2(acr);
-                        acr += tot[J][e];       // the next (smaller) J also crosses sub-block J
-                    } else fr[J][e] = 0.f;
-                }
+                for (int J = 3; J >= 0; J--)
+                    if (J < I) {
+                        f[J * 32] = ex2(acr);
+                        acr += tot[J];          // the next (smaller) J also crosses sub-block J
+                    }
             }
+            __syncwarp();
+            auto ldfac = [&](int slot, float (&v)[4]) {
+                const float4 t = *reinterpret_cast<const float4*>(fac + slot * 32 + 4 * cq);
+                v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+            };
+            ldfac(I, ebt);                      // 2^(total of the own sub-block)
+            {                                   // K side: needed by the P^T MMAs
+                float ko[4][4];
 #pragma unroll
-            for (int r = 0; r < 4; r++) {       // K side: needed by the P^T MMAs
-                const int off = sw_chunk(rows[r], cchunk) + coff;
-                float ko[4], x4[4];
-                up4bf(kpk[r], ko);
+                for (int r = 0; r < 4; r++) {
+                    up4bf(kpk[r], ko[r]);
 #pragma unroll
-                for (int e = 0; e < 4; e++) ko[e] *= ei[r][e];
+                    for (int e = 0; e < 4; e++) ko[r][e] *= ei[r][e];
+                }
 #pragma unroll
                 for (int m = 0; m < 4; m++) {
                     if (m >= I) {               // target variant I' = m + 1 (I' = 4 -> Kend)
+                        float f[4], x4[4];
+                        ldfac(m, f);
 #pragma unroll
-                        for (int e = 0; e < 4; e++) x4[e] = ko[e] * fk[m][e];
-                        // low-order halves only where the gw cancellation needs them: variant I' = I + 1 (and the own
-                        // variant, phase 1); farther variants are damped by at least one whole sub-block of decay
-                        if (m == 3) st4bf(kend + off, x4);
-                        else if (m == I) st4bf_hilo(sm.kt + vbK[m + 1] + off, sm.kt_lo + vbK[m + 1] + off, x4);
-                        else st4bf(sm.kt + vbK[m + 1] + off, x4);
+                        for (int r = 0; r < 4; r++) {
+                            const int off = sw_chunk(rows[r], cchunk) + coff;
+#pragma unroll
+                            for (int e = 0; e < 4; e++) x4[e] = ko[r][e] * f[e];
+                            // low-order halves only where the gw cancellation needs them: variant I' = I + 1 (and the own
+                            // variant, phase 1); farther variants are damped by at least one whole sub-block of decay
+                            if (m == 3) st4bf(kend + off, x4);
+                            else if (m == I) st4bf_hilo(sm.kt + vbK[m + 1] + off, sm.kt_lo + vbK[m + 1] + off, x4);
+                            else st4bf(sm.kt + vbK[m + 1] + off, x4);
+                        }
                     }
                 }
             }
@@ -447,24 +471,34 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
             __syncwarp();
             if (tid == 0 && cb + 1 < nloc) issue_rkw(cb + 1);
+            {                                   // R side: needed by the phase-2 MMAs only
+                float ro[4][4], fst[4];
+                ldfac(5, fst);
 #pragma unroll
-            for (int r = 0; r < 4; r++) {       // R side: needed by the phase-2 MMAs only
-                const int off = sw_chunk(rows[r], cchunk) + coff;
-                float ro[4], x4[4];
-                up4bf(rpk[r], ro);
+                for (int r = 0; r < 4; r++) {
+                    const int off = sw_chunk(rows[r], cchunk) + coff;
+                    float x4[4];
+                    up4bf(rpk[r], ro[r]);
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    ro[e] *= eo[r][e];
-                    x4[e] = ro[e] * fst[e];
+                    for (int e = 0; e < 4; e++) {
+                        ro[r][e] *= eo[r][e];
+                        x4[e] = ro[r][e] * fst[e];
+                    }
+                    st4bf_hilo(sm.rst + off, sm.rst_lo + off, x4);
                 }
-                st4bf_hilo(sm.rst + off, sm.rst_lo + off, x4);
 #pragma unroll
                 for (int J = 0; J < 4; J++) {
                     if (J <= I) {
+                        float f[4], x4[4];
+                        ldfac(J == I ? 4 : J, f);
 #pragma unroll
-                        for (int e = 0; e < 4; e++) x4[e] = ro[e] * fr[J][e];
-                        if (J + 1 >= I) st4bf_hilo(sm.rp + vbR[J] + off, sm.rp_lo + vbR[J] + off, x4);   // own / previous sub-block
-                        else st4bf(sm.rp + vbR[J] + off, x4);
+                        for (int r = 0; r < 4; r++) {
+                            const int off = sw_chunk(rows[r], cchunk) + coff;
+#pragma unroll
+                            for (int e = 0; e < 4; e++) x4[e] = ro[r][e] * f[e];
+                            if (J + 1 >= I) st4bf_hilo(sm.rp + vbR[J] + off, sm.rp_lo + vbR[J] + off, x4);   // own / previous sub-block
+                            else st4bf(sm.rp + vbR[J] + off, x4);
+                        }
                     }
                 }
             }
@@ -707,9 +741,6 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             const float4 hA = *reinterpret_cast<const float4*>(&sm.hst[0][c0]);
             const float4 hB = *reinterpret_cast<const float4*>(&sm.hst[1][c0]);
             const float hs[4] = {hA.x + hB.x, hA.y + hB.y, hA.z + hB.z, hA.w + hB.w};
-            float ebt[4];
-#pragma unroll
-            for (int e = 0; e < 4; e++) ebt[e] = ex2(bt[e]);
 #pragma unroll
             for (int r = 0; r < 4; r++) {
                 const int row = rows[r];
