@@ -326,6 +326,9 @@ static int run_backward(int dtype, int B, int T, int C, int H, const BwdSet* set
         e = -1;
         if (ws && aligned16(ws) && ws_bytes > soff)
             e = launch_bwd_chunk_segmented(p, reinterpret_cast<char*>(ws) + soff, ws_bytes - soff, (cudaStream_t)stream);
+        // more sequences than SMs: balanced persistent grid with hand-over records in the same scratch
+        if (e < 0 && ws && aligned16(ws) && ws_bytes > soff)
+            e = launch_bwd_chunk_balanced(p, reinterpret_cast<char*>(ws) + soff, ws_bytes - soff, (cudaStream_t)stream);
         if (e < 0) e = launch_bwd_chunk(p, (cudaStream_t)stream);
         return cuda_fail(e, "wkv6 chunk backward launch");
     }

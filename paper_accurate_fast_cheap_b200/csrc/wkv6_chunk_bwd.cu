@@ -24,7 +24,9 @@
 //   phase 1:  Q = G V^T;  P^T (4 x N16, as forward G1);  RS^T[j][p] = S0^T G^T;  KC^T[j][q] = C^T V^T
 //   phase 2:  R^T[j][p in I] = Ktil(I)^T Qm^T (4 x N16);  K^T[j][q in J] = Rtil'(J)^T Qm (4 x N16);
 //             GV[q][i] = P^T G + Kend C^T;  dC^T[j][i] = Rst^T G
-// 8 accumulators x 64 columns = all 512 TMEM columns -> one CTA (256 threads) per SM.
+// 8 accumulators x 64 columns = all 512 TMEM columns -> one CTA per SM: 512 threads (16 warps, 128 registers each), so
+// that every scheduler of the SM has four warps to hide the latencies of the elementwise phases with.
+#include <chrono>
 #include "wkv6_fwd_tiles.cuh"
 
 namespace wkv6 {
@@ -52,17 +54,19 @@ struct BwdChunkSmem {
     alignas(1024) uint8_t o_gw[CL * 128];    // staging tile of gw (TMA store)
     float blocktot[4][N];                    // log2 decay sums of the four sub-blocks (direction order), per channel
     float dtot[4][N];                        // sub-block sums of (k gkC - r grS), per channel
-    float hst[2][N];                         // S_0 . C_0 partial sums (two column halves)
-    float bonus[2][CL];                      // sum_j r u k per row (two channel halves)
+    float hst[4][N];                         // S_0 . C_0 partial sums (four column quarters)
+    float bonus[4][CL];                      // sum_j r u k per row (four channel quarters)
     float vg[CL];                            // v_p . gy_p per row
-    float gured[8][N / 2];
+    float gured[16][N / 4];
     alignas(8) uint64_t bar_rkw, bar_vg[2], bar_sp, bar_m1, bar_mp, bar_m2, bar_m2b;
     uint32_t tmem_base;
 };
 static_assert(sizeof(BwdChunkSmem) <= 226 * 1024, "shared memory budget");
 static_assert(CL * XSTR * 4 <= 20 * 1024, "xk must fit into the rp region");
 
-__global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_constant__ Params p) {
+constexpr int kBwdThreads = 512;
+
+__global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __grid_constant__ Params p) {
     extern __shared__ __align__(1024) uint8_t smem_bytes[];
     // offset arithmetic on the __shared__ array (not a uintptr_t round trip) keeps the address space visible to the
     // compiler: LDS/STS instead of generic LD/ST
@@ -74,19 +78,65 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     // turns every UTCHMMA into a waterfall loop of R2UR broadcasts)
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int BH = p.B * p.H;
-    // time-segmented launch (launch_bwd_chunk_segmented below): CTA = (sequence, segment), segments in PROCESSING order
-    // (segment 0 holds the chunks the reverse sweep visits first); unsegmented: nseg = 1
-    const int nseg = p.nseg > 1 ? p.nseg : 1;
-    const int seq = blockIdx.x / nseg, seg = blockIdx.x - seq * nseg;
-    const int ds = seq / BH;
-    const int bh = seq - ds * BH;
-    const int b = bh / p.H, h = bh - b * p.H;
-    const DirArgs& D = p.d[ds];
-    const bool rev = D.reverse != 0;
     const int T = p.T;
     const int nchunks = (T + CL - 1) / CL;
-    const int cbeg = nseg > 1 ? seg * p.seg_chunks : 0;                 // this CTA sweeps chunks cbeg .. cbeg + nloc - 1
-    const int nloc = nseg > 1 ? min(p.seg_chunks, nchunks - cbeg) : nchunks;   // (processing order)
+    // ---- the CTA's schedule: a list of "pieces" (runs of consecutive chunks of one sequence, in PROCESSING order: chunk 0 is
+    // the one the reverse sweep visits first), walked by ONE flat loop over chunks so that the loads of the next chunk are
+    // in flight across piece boundaries.  Three launch shapes:
+    //  * one CTA per sequence (grid = sequences): a single piece of kind W (whole sequence);
+    //  * time-segmented (launch_bwd_chunk_segmented below; nseg > 1): CTA = (sequence, segment), a single piece of kind SEG
+    //    that starts from the segment scan's state and leaves a partial gu;
+    //  * balanced persistent grid (launch_bwd_chunk_balanced; bal_ncta > 0): every direction's (sequence, chunk) units are cut
+    //    into bal_ncta equal contiguous ranges, one CTA each.  A range = [B: rest of a sequence another CTA began]
+    //    [whole sequences] [A: first part of a sequence the next CTA finishes]; the CTA runs A FIRST and hands the reverse
+    //    state and the partial gu over through a record in the scratch (data, __threadfence, flag = the launch's epoch with
+    //    release semantics), then the whole sequences, and B LAST (acquire on the previous CTA's record, which was written
+    //    right at that CTA's start): nobody waits for long, and with blocks dispatched in index order never forever.
+    // The unit (sequence, chunk) of iteration `it` is a closed-form function of the loop counter and CTA constants -- no
+    // loop-carried schedule state, divisions by multiplication with host-made reciprocals -- so that ptxas keeps every TMA
+    // coordinate in uniform registers (loop-carried state ended up in vector registers: every TMA issue a waterfall loop).
+    enum { kA = 0, kW = 1, kB = 2, kSEG = 3 };
+    const int nseg = p.nseg > 1 ? p.nseg : 1;
+    int ds, seq = 0, seg = 0, nunits;
+    int bhA = 0, lenA = 0, bhW = 0, nW = 0, bhB = 0, cB0 = 0;
+    if (p.bal_ncta > 0) {
+        ds = blockIdx.x / p.bal_ncta;
+        const unsigned j = blockIdx.x - ds * p.bal_ncta, U = (unsigned)(BH * nchunks);    // (j + 1) U < 2^31: pick_balanced
+        const int gs = (int)(j * U / (unsigned)p.bal_ncta), ge = (int)((j + 1) * U / (unsigned)p.bal_ncta);
+        const int gsu = min((gs + nchunks - 1) / nchunks * nchunks, ge), ged = max(ge / nchunks * nchunks, gsu);
+        bhA = ged / nchunks; lenA = ge - ged;
+        bhW = gsu / nchunks; nW = (ged - gsu) / nchunks;
+        bhB = gs / nchunks;  cB0 = gs - bhB * nchunks;          // B exists when gsu > gs
+        nunits = ge - gs;
+    } else {
+        seq = blockIdx.x / nseg; seg = blockIdx.x - seq * nseg;
+        ds = seq / BH;
+        bhB = seq - ds * BH;                                    // one piece, in the B slot: chunks cB0 .. cB0 + nunits - 1
+        cB0 = nseg > 1 ? seg * p.seg_chunks : 0;
+        nunits = nseg > 1 ? min(p.seg_chunks, nchunks - cB0) : nchunks;
+    }
+    const int lenW = nW * nchunks;
+    const int stageB = p.bal_ncta > 0 ? kB : nseg > 1 ? kSEG : kW;
+    struct Unit { int stage, bh, b, h, c; };                    // c: chunk of the sequence in processing order
+    auto udiv = [](int x, unsigned magic) { return (int)(((unsigned long long)(unsigned)x * magic) >> 31); };   // x / d, magic = 2^31 / d + 1
+    auto unit_at = [&](int it) {
+        Unit u;
+        const int x = it - lenA;
+        const int iw = udiv(max(x, 0), p.bal_magic_n);
+        u.stage = x < 0 ? kA : x < lenW ? kW : stageB;
+        u.bh = x < 0 ? bhA : x < lenW ? bhW + iw : bhB;
+        u.c = x < 0 ? it : x < lenW ? x - iw * nchunks : cB0 + (x - lenW);
+        u.b = udiv(u.bh, p.bal_magic_h);
+        u.h = u.bh - u.b * p.H;
+        return u;
+    };
+    const Unit cu0 = unit_at(0);
+    const DirArgs& D = p.d[ds];
+    const bool rev = D.reverse != 0;
+    // hand-over records of the balanced grid: [64 i][64 j] reverse state, [64] partial gu, flag
+    constexpr size_t kRecBytes = (size_t)N * N * 4 + 512;
+    uint8_t* const rec_in = p.bal_rec + (size_t)blockIdx.x * kRecBytes;    // written by CTA blockIdx.x - 1 (its piece A)
+    uint8_t* const rec_out = rec_in + kRecBytes;
 
     // compact variant tiles: virtual base (row 0) of every variant inside sm.kt / sm.rp
     const int vbK[4] = {rev ? 12288 : 0, rev ? 10240 : 2048, 6144, rev ? 0 : 12288};   // Ktil(I): sub-blocks <= I
@@ -127,73 +177,59 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         // reverse-state load), not after it
         fence_proxy_async();
         pdl_wait();
-        if (nloc > 0) {
-            const int q0 = rev ? cbeg : nchunks - 1 - cbeg;   // tile of the chunk this CTA's reverse sweep starts with
+        if (nunits > 0) {
+            const int q0 = rev ? cu0.c : nchunks - 1 - cu0.c;   // tile of the chunk this CTA's reverse sweep starts with
             mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
-            tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q0 * CL, b);
-            tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q0 * CL, b);
-            tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q0 * CL, b);
+            tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, cu0.h * N, q0 * CL, cu0.b);
+            tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, cu0.h * N, q0 * CL, cu0.b);
+            tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, cu0.h * N, q0 * CL, cu0.b);
             mbar_arrive_expect_tx(&sm.bar_vg[0], 2u * CL * 128);
-            tma_load_3d(sm.v[0], &D.mv, &sm.bar_vg[0], h * N, q0 * CL, b);
-            tma_load_3d(sm.g[0], &D.mg, &sm.bar_vg[0], h * N, q0 * CL, b);
+            tma_load_3d(sm.v[0], &D.mv, &sm.bar_vg[0], cu0.h * N, q0 * CL, cu0.b);
+            tma_load_3d(sm.g[0], &D.mg, &sm.bar_vg[0], cu0.h * N, q0 * CL, cu0.b);
             mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
-            tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1 - cbeg)) * N);
+            tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (cu0.bh * nchunks + (nchunks - 1 - cu0.c)) * N);
         }
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    for (int i = tid; i < 28 * 1024 / 16; i += 256) reinterpret_cast<uint4*>(sm.kt)[i] = make_uint4(0, 0, 0, 0);
-    for (int i = tid; i < 20 * 1024 / 16; i += 256) reinterpret_cast<uint4*>(sm.rp)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < 28 * 1024 / 16; i += kBwdThreads) reinterpret_cast<uint4*>(sm.kt)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < 20 * 1024 / 16; i += kBwdThreads) reinterpret_cast<uint4*>(sm.rp)[i] = make_uint4(0, 0, 0, 0);
 
-    // ---- fragment coordinates (TMEM 16x256b.x4): rows frow, frow+8; columns fcol + 8*rep + {0,1}, rep = 0..3
-    const int qtr = warp & 3, half = warp >> 2;
+    // ---- fragment coordinates (TMEM 16x256b.x2): warp = (lane quarter qtr, column quarter cqt): one 16x16 block of an
+    // accumulator; rows frow, frow+8; columns fcol + 8*rep + {0,1}, rep = 0..1
+    const int qtr = warp & 3, cqt = warp >> 2;
     const int frow = 16 * qtr + (lane >> 2);
-    const int fcol = 32 * half + 2 * (lane & 3);
+    const int fcol = 16 * cqt + 2 * (lane & 3);
     const uint32_t lane_field = (uint32_t)(qtr * 32) << 16;
-    // stmatrix row addresses of this lane for a 16x32 fragment (two x4 stores; matrix k = lane>>3 of store s is
-    // rep = 2s + (k>>1), hh = k&1): stoff = the fragment as it is, ttoff = its transpose (rows = fragment columns)
-    uint32_t stoff[2], ttoff[2];
+    // stmatrix row address of this lane for the 16x16 fragment (one x4 store; matrix k = lane>>3 is rep = k>>1,
+    // hh = k&1): stoff = the fragment as it is, ttoff = its transpose (rows = fragment columns)
+    uint32_t stoff, ttoff;
     {
         const int k = lane >> 3, r8 = lane & 7;
-        const int row = 16 * qtr + 8 * (k & 1) + r8;
-        stoff[0] = (uint32_t)sw_chunk(row, 4 * half + (k >> 1));
-        stoff[1] = (uint32_t)sw_chunk(row, 4 * half + 2 + (k >> 1));
-        ttoff[0] = (uint32_t)sw_chunk(32 * half + 8 * (k >> 1) + r8, 2 * qtr + (k & 1));
-        ttoff[1] = (uint32_t)sw_chunk(32 * half + 16 + 8 * (k >> 1) + r8, 2 * qtr + (k & 1));
+        stoff = (uint32_t)sw_chunk(16 * qtr + 8 * (k & 1) + r8, 2 * cqt + (k >> 1));
+        ttoff = (uint32_t)sw_chunk(16 * cqt + 8 * (k >> 1) + r8, 2 * qtr + (k & 1));
     }
     const int sgn = rev ? -1 : 1;
     const int dfrag = sgn * ((lane >> 2) - 2 * (lane & 3));   // sgn * (row - column) of fragment element (rep 0, hh 0, e 0)
 
-    // ---- row-major coordinates (preprocessing / final epilogue): sub-block I (direction order), 4 rows x 4 channels
+    // ---- row-major coordinates (preprocessing / final epilogue): sub-block I (direction order), 4 rows x 2 channels
     const int I = warp & 3, ch = warp >> 2;
     const int cq = lane & 7, rg = lane >> 3;
-    const int c0 = 32 * ch + 4 * cq;
+    const int c0 = 16 * ch + 2 * cq;
     const int coff = (c0 & 7) * 2, cchunk = c0 >> 3;
+    const int row0 = rev ? 63 - (16 * I + 4 * rg) : 16 * I + 4 * rg;   // the thread's rows: row0 + sgn * r, r = 0..3
     const int vbK_own = I == 0 ? vbK[0] : I == 1 ? vbK[1] : I == 2 ? vbK[2] : vbK[3];
 
     pdl_wait();   // first global access below (see wkv6_common.cuh)
-    float u4[4];
-    ld4bf(reinterpret_cast<const uint8_t*>(D.u) + (h * N + c0) * 2, u4);
-    float gu4[4] = {0.f, 0.f, 0.f, 0.f};
-
+    float u4[2];
+    float gu4[2];
     // reverse state C^T[j][i]: j = frow + 8*hh, i = fcol + 8*rep + e  ->  cs[4*rep + 2*hh + e]
-    float cs[16];
-    {
-        // start of the sweep: the gradient into S_T; a later segment starts from what the segment scan left in its slot
-        const float* g0 = nseg > 1 ? p.seg_state + ((size_t)seq * nseg + seg) * N * N : D.gsT ? D.gsT + (size_t)bh * N * N : nullptr;
-#pragma unroll
-        for (int rep = 0; rep < 4; rep++)
-#pragma unroll
-            for (int hh = 0; hh < 2; hh++)
-#pragma unroll
-                for (int e = 0; e < 2; e++)
-                    cs[4 * rep + 2 * hh + e] = g0 ? g0[(fcol + 8 * rep + e) * N + frow + 8 * hh] : 0.f;
-    }
+    float cs[8];
     auto store_cp = [&]() {
 #pragma unroll
-        for (int rep = 0; rep < 4; rep++)
+        for (int rep = 0; rep < 2; rep++)
 #pragma unroll
             for (int hh = 0; hh < 2; hh++) {
                 const int col = fcol + 8 * rep;
@@ -201,8 +237,85 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     pack_bf16(cs[4 * rep + 2 * hh], cs[4 * rep + 2 * hh + 1]);
             }
     };
-    store_cp();
-    fence_proxy_async();
+    // start of a piece: the reverse state (gradient into S_T / what the segment scan left in the slot / the record the
+    // previous CTA handed over), u of the head, gu = 0, bf16 copy of the state for the first chunk's MMAs
+    auto piece_start = [&](const Unit& u) {
+        const float* g0;
+        if (u.stage == kSEG) g0 = p.seg_state + ((size_t)seq * nseg + seg) * N * N;
+        else if (u.stage == kB) {
+            if (tid == 0) {
+                const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(rec_in + (size_t)N * N * 4 + 256);
+                unsigned long long v = 0;
+                long long spins = 0;
+                for (;;) {
+                    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
+                    if (v == p.bal_epoch) break;
+                    if (++spins > (1ll << 25)) __trap();          // seconds: the producer died
+                    __nanosleep(100);
+                }
+            }
+            __syncthreads();
+            g0 = reinterpret_cast<const float*>(rec_in);
+        } else g0 = D.gsT ? D.gsT + (size_t)u.bh * N * N : nullptr;
+#pragma unroll
+        for (int rep = 0; rep < 2; rep++)
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                for (int e = 0; e < 2; e++)
+                    cs[4 * rep + 2 * hh + e] = g0 ? __ldcg(g0 + (fcol + 8 * rep + e) * N + frow + 8 * hh) : 0.f;
+        up2bf(*reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(D.u) + (u.h * N + c0) * 2), u4);
+        gu4[0] = gu4[1] = 0.f;
+        store_cp();
+        fence_proxy_async();
+    };
+    // end of a piece: gu (final, per-segment partial, or partial into the hand-over record), the reverse state (gs0 when the
+    // sweep reached the sequence's first step, or the hand-over record followed by its flag)
+    auto piece_end = [&](const Unit& u) {
+        // gu[b][h*64 + c] = sum over rows of r k (v.gy): row groups by shuffle, sub-blocks through smem
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            gu4[e] += __shfl_xor_sync(0xffffffffu, gu4[e], 8);
+            gu4[e] += __shfl_xor_sync(0xffffffffu, gu4[e], 16);
+        }
+        if (rg == 0) {
+#pragma unroll
+            for (int e = 0; e < 2; e++) sm.gured[warp][2 * cq + e] = gu4[e];
+        }
+        float* sout = nullptr;
+        if (u.stage == kA) sout = reinterpret_cast<float*>(rec_out);
+        else if (D.gs0 && (u.stage != kSEG || seg == nseg - 1)) sout = D.gs0 + (size_t)u.bh * N * N;   // the sequence's first step
+        if (sout) {
+#pragma unroll
+            for (int rep = 0; rep < 2; rep++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++)
+#pragma unroll
+                    for (int e = 0; e < 2; e++) sout[(fcol + 8 * rep + e) * N + frow + 8 * hh] = cs[4 * rep + 2 * hh + e];
+        }
+        __syncthreads();
+        if (tid < N) {
+            const int hc = tid >> 4, cc = tid & 15;   // warp = sub-block + 4 * (16-channel quarter)
+            float g = sm.gured[4 * hc + 0][cc] + sm.gured[4 * hc + 1][cc] + sm.gured[4 * hc + 2][cc] + sm.gured[4 * hc + 3][cc];
+            if (u.stage == kB) g += __ldcg(reinterpret_cast<const float*>(rec_in + (size_t)N * N * 4) + tid);
+            if (u.stage == kA) reinterpret_cast<float*>(rec_out + (size_t)N * N * 4)[tid] = g;
+            else if (u.stage == kSEG) p.seg_gu[((size_t)seq * nseg + seg) * N + tid] = g;      // summed by wkv6_bwd_seg_gu_kernel
+            else reinterpret_cast<__nv_bfloat16*>(D.gu)[(size_t)u.b * p.C + u.h * N + tid] = __float2bfloat16_rn(g);
+        }
+        // (the barrier is unconditional: a CTA barrier under the stage test cost ptxas the uniformity of the whole chunk loop)
+        if (u.stage == kA) __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            if (u.stage == kA) {
+                unsigned long long* flag = reinterpret_cast<unsigned long long*>(rec_out + (size_t)N * N * 4 + 256);
+                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(flag), "l"(p.bal_epoch) : "memory");
+            } else if (u.stage == kB) {
+                // consumed: the flag goes back to 0, so that a replay of the same launch (CUDA graph: same epoch) waits again
+                *reinterpret_cast<volatile unsigned long long*>(rec_in + (size_t)N * N * 4 + 256) = 0ull;
+            }
+        }
+    };
+    if (nunits > 0) piece_start(cu0);
 
     tc_fence_before();
     __syncthreads();
@@ -225,23 +338,24 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     // Loads of the next chunk are issued as soon as their landing tiles are dead: r/k/w after the operand tiles are
     // built (r, k live on in registers), v/gy after the phase-2 MMAs, the checkpoint after the anchor sum.
     // (cb = local chunk counter of this CTA, 0 .. nloc - 1; cbeg + cb = chunk in the sequence's processing order)
-    auto tile_q = [&](int cb) { const int c = nchunks - 1 - (cbeg + cb); return rev ? nchunks - 1 - c : c; };
-    auto issue_rkw = [&](int cb) {   // thread 0 only
-        const int q = tile_q(cb);
+    // (it = chunk counter of this CTA, 0 .. nunits - 1; Unit::c = chunk in its sequence's processing order)
+    auto tile_q = [&](const Unit& u) { return rev ? u.c : nchunks - 1 - u.c; };
+    auto issue_rkw = [&](const Unit& u) {   // thread 0 only
+        const int q = tile_q(u);
         mbar_arrive_expect_tx(&sm.bar_rkw, 3u * CL * 128);
-        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, h * N, q * CL, b);
-        tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, h * N, q * CL, b);
-        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, h * N, q * CL, b);
+        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_rkw, u.h * N, q * CL, u.b);
+        tma_load_3d(sm.raw_k, &D.mk, &sm.bar_rkw, u.h * N, q * CL, u.b);
+        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_rkw, u.h * N, q * CL, u.b);
     };
-    auto issue_vg = [&](int cb) {
-        const int q = tile_q(cb);
-        mbar_arrive_expect_tx(&sm.bar_vg[cb & 1], 2u * CL * 128);
-        tma_load_3d(sm.v[cb & 1], &D.mv, &sm.bar_vg[cb & 1], h * N, q * CL, b);
-        tma_load_3d(sm.g[cb & 1], &D.mg, &sm.bar_vg[cb & 1], h * N, q * CL, b);
+    auto issue_vg = [&](const Unit& u, int buf) {
+        const int q = tile_q(u);
+        mbar_arrive_expect_tx(&sm.bar_vg[buf], 2u * CL * 128);
+        tma_load_3d(sm.v[buf], &D.mv, &sm.bar_vg[buf], u.h * N, q * CL, u.b);
+        tma_load_3d(sm.g[buf], &D.mg, &sm.bar_vg[buf], u.h * N, q * CL, u.b);
     };
-    auto issue_sp = [&](int cb) {
+    auto issue_sp = [&](const Unit& u) {
         mbar_arrive_expect_tx(&sm.bar_sp, (uint32_t)N * 128);
-        tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (bh * nchunks + (nchunks - 1 - (cbeg + cb))) * N);
+        tma_load_2d(sm.sp, &D.mc, &sm.bar_sp, 0, (u.bh * nchunks + (nchunks - 1 - u.c)) * N);
     };
     // (the loads of the first chunk were issued at the top of the prologue)
 
@@ -251,19 +365,21 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
     constexpr uint32_t ID_KM64 = umma_idesc(0, 1, 64, 64);
     constexpr uint32_t ID_MM64 = umma_idesc(1, 1, 64, 64);
 
-    for (int cb = 0; cb < nloc; cb++) {
-        const int c = nchunks - 1 - (cbeg + cb);         // chunk index in the direction's own order
-        const int q = rev ? nchunks - 1 - c : c;         // tile index in memory
-        const int t0 = q * CL;
+    for (int cb = 0; cb < nunits; cb++) {
+        const Unit cu = unit_at(cb);
+        const bool more = cb + 1 < nunits;
+        const Unit nu = unit_at(cb + 1);                 // the chunk after this one (if `more`)
+        const int t0 = tile_q(cu) * CL;                  // first step of the chunk's tile in memory
         const uint32_t par = cb & 1;
         const uint64_t vgoff = (cb & 1) ? DOFF(CL * 128) : 0;   // V / G buffer of this chunk (v[1] - v[0] = g[1] - g[0] = 8 KB)
         const uint64_t dk_g = dk_g0 + vgoff, dk_v = dk_v0 + vgoff, dm_g = dm_g0 + vgoff;
         const int c_ts = cb;
+        if (wkv6_trace_on && tid == 0 && cb < 32) p.dbg[96 + cb] = clock64();   // loop-top stamp of every chunk (debug trace)
         WKV6_TS(64, 0);
         // staging tiles of the previous chunk have been read (they alias operand tiles that are rewritten after the next
         // CTA-wide barrier).  The store thread is warp 7 lane 0: it issues no MMAs, so this wait delays nobody.
         if (tid == 224) tma_store_wait_read<0>();
-        if (tid == 0 && cb + 1 < nloc) issue_vg(cb + 1);   // other V / G buffer: its readers finished last iteration
+        if (tid == 0 && more) issue_vg(nu, (cb + 1) & 1);   // other V / G buffer: its readers finished last iteration
         if (warp < 3 && elect_one()) {
             // ---- MMA phase 1a: everything that needs no preprocessing (V, G, S_0, C are raw / carried tiles)
             mbar_wait(&sm.bar_vg[cb & 1], (cb >> 1) & 1);
@@ -286,28 +402,28 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         // ================= phase 1: decays, in-block cumulative sums, Rtil, Ktil(own), bonus
         mbar_wait(&sm.bar_rkw, par);
         WKV6_TS(64, 1);
-        float eo[4][4], ei[4][4], ew[4][4], ebt[4];           // ebt = 2^(log2 decay total of the own sub-block)
-        uint2 rpk[4], kpk[4];                            // this thread's r and k (bf16 x4 per row) for the later phases
-        int rows[4];
+        float eo[4][2], ei[4][2], ew[4][2], ebt[2];           // ebt = 2^(log2 decay total of the own sub-block)
+        uint32_t rpk[4], kpk[4];                         // this thread's r and k (bf16 x2 per row) for the later phases
+        int offs[4];                                     // byte offsets of the thread's four (row, channel pair) words in a tile
         {
-            float rr[4][4], kk[4][4], l2[4][4], dstep[4][4], bsum[4];
+            float rr[4][2], kk[4][2], l2[4][2], dstep[4][2], bsum[4];
             float xmax = 0.f;
 #pragma unroll
             for (int r = 0; r < 4; r++) {
                 const int pos = 16 * I + 4 * rg + r;
                 const int row = rev ? 63 - pos : pos;
-                rows[r] = row;
                 const int off = sw_chunk(row, cchunk) + coff;
-                float w4[4];
-                rpk[r] = *reinterpret_cast<const uint2*>(sm.raw_r + off);
-                kpk[r] = *reinterpret_cast<const uint2*>(sm.raw_k + off);
-                up4bf(rpk[r], rr[r]);
-                up4bf(kpk[r], kk[r]);
-                ld4bf(sm.raw_w + off, w4);
+                offs[r] = off;
+                float w4[2];
+                rpk[r] = *reinterpret_cast<const uint32_t*>(sm.raw_r + off);
+                kpk[r] = *reinterpret_cast<const uint32_t*>(sm.raw_k + off);
+                up2bf(rpk[r], rr[r]);
+                up2bf(kpk[r], kk[r]);
+                up2bf(*reinterpret_cast<const uint32_t*>(sm.raw_w + off), w4);
                 const bool valid = t0 + row < T;
                 float bs = 0.f;
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
+                for (int e = 0; e < 2; e++) {
                     bs = fmaf(rr[r][e] * u4[e], kk[r][e], bs);
                     const float x = ex2(w4[e] * kLog2e);            // exp(w)
                     ew[r][e] = x;
@@ -325,20 +441,20 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 #pragma unroll
                 for (int r = 0; r < 4; r++)
 #pragma unroll
-                    for (int e = 0; e < 4; e++) {
+                    for (int e = 0; e < 2; e++) {
                         const float x = fminf(ew[r][e], 1e30f);
                         ew[r][e] = x * ex2(fminf(kClampL2 - x * kLog2e, 0.f));
                     }
             }
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
+            for (int e = 0; e < 2; e++) {
                 l2[1][e] += l2[0][e];
                 l2[2][e] += l2[1][e];
                 l2[3][e] += l2[2][e];
             }
-            float excl[4];
+            float excl[2];
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
+            for (int e = 0; e < 2; e++) {
                 float x = l2[3][e];
                 float y = __shfl_up_sync(0xffffffffu, x, 8);
                 if (rg >= 1) x += y;
@@ -351,7 +467,7 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             // and products of the step decays in between (the MUFU pipe, 16 lanes per clock per SM, bounds this phase: 6 ex2
             // per channel instead of 8)
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
+            for (int e = 0; e < 2; e++) {
                 eo[0][e] = ex2(excl[e]);
                 eo[1][e] = eo[0][e] * dstep[0][e];
                 eo[2][e] = eo[1][e] * dstep[1][e];
@@ -363,20 +479,19 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
 #pragma unroll
             for (int r = 0; r < 4; r++) {
-                float ro[4], ko[4];
+                float ro[2], ko[2];
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
+                for (int e = 0; e < 2; e++) {
                     ro[e] = rr[r][e] * eo[r][e];
                     ko[e] = kk[r][e] * ei[r][e];
                 }
-                const int off = sw_chunk(rows[r], cchunk) + coff;
-                st4bf(sm.roff + off, ro);
-                st4bf_hilo(sm.kt + vbK_own + off, sm.kt_lo + vbK_own + off, ko);
+                st2bf(sm.roff + offs[r], ro);
+                st2bf_hilo(sm.kt + vbK_own + offs[r], sm.kt_lo + vbK_own + offs[r], ko);
                 float bs = bsum[r];
                 bs += __shfl_xor_sync(0xffffffffu, bs, 1);
                 bs += __shfl_xor_sync(0xffffffffu, bs, 2);
                 bs += __shfl_xor_sync(0xffffffffu, bs, 4);
-                if (cq == 0) sm.bonus[ch][rows[r]] = bs;
+                if (cq == 0) sm.bonus[ch][row0 + sgn * r] = bs;
             }
         }
         WKV6_TS(64, 2);
@@ -385,69 +500,69 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         // ================= phase 1b: cross-block factors -> Rst, Ktil(I' > I), Kend, Rtil'(J <= I)
         {
             // Six factors per channel: fst = 2^(a_I);  fk[m] = 2^(a_{m+1} - a_I), m >= I (m = 3: chunk end);  fr[J] = 2^(a_I - a_{J+1}),
-            // J <= I.  The four row groups of a warp work on the same channels: lane (rg, cq) computes the six of channel c0 + rg and
-            // the warp exchanges them through 768 bytes of the gw staging tile (idle until the final epilogue; its TMA store
-            // was waited for at the top of the chunk): 6 ex2 per lane instead of 36 -- the MUFU pipe bounds this phase.
-            // Slots [6][32 channels]: m < I: fr[m];  m >= I: fk[m];  4: fr[I];  5: fst.
-            float* const fac = reinterpret_cast<float*>(sm.o_gw) + warp * 192;
+            // J <= I.  The four row groups of a warp work on the same 16 channels: lane l computes three of the six of channel
+            // 16 ch + (l & 15) and the warp exchanges them through 384 bytes of the gw staging tile (idle until the final
+            // epilogue; its TMA store was waited for at the top of the chunk): 3 ex2 per lane instead of 12 -- the MUFU pipe
+            // bounds this phase.  Slots [6][16 channels]: m < I: fr[m];  m >= I: fk[m];  4: fr[I];  5: fst.
+            float* const fac = reinterpret_cast<float*>(sm.o_gw) + warp * 96;
             {
+                const int cw = lane & 15, part = lane >> 4;
                 float tot[4];
 #pragma unroll
-                for (int m = 0; m < 4; m++) tot[m] = sm.blocktot[m][c0 + rg];
+                for (int m = 0; m < 4; m++) tot[m] = sm.blocktot[m][16 * ch + cw];
+                // slot m < 4: m >= I: sum_{x = I..m} tot[x];  m < I: sum_{x = m+1..I-1} tot[x]
+                auto slot_exp = [&](int m) {
+                    float a = 0.f;
+#pragma unroll
+                    for (int x = 0; x < 4; x++)
+                        if (m >= I ? (x >= I && x <= m) : (x > m && x < I)) a += tot[x];
+                    return a;
+                };
                 float pre = 0.f, totI = tot[0];
 #pragma unroll
                 for (int m = 0; m < 4; m++) {
                     if (m < I) pre += tot[m];
                     if (m == I) totI = tot[m];
                 }
-                float* const f = fac + 4 * cq + rg;
-                f[5 * 32] = ex2(pre);
-                f[4 * 32] = ex2(-totI);
-                float acc = 0.f;
-#pragma unroll
-                for (int m = 0; m < 4; m++)
-                    if (m >= I) {               // target variant I' = m + 1
-                        acc += tot[m];
-                        f[m * 32] = ex2(acc);
-                    }
-                // fr[J], J < I: exponent a_I - a_{J+1} = 0 (J = I-1), sum_{m=J+1}^{I-1} tot[m] otherwise
-                float acr = 0.f;
-#pragma unroll
-                for (int J = 3; J >= 0; J--)
-                    if (J < I) {
-                        f[J * 32] = ex2(acr);
-                        acr += tot[J];          // the next (smaller) J also crosses sub-block J
-                    }
+                float* const f = fac + cw;
+                if (part == 0) {
+                    f[0 * 16] = ex2(slot_exp(0));
+                    f[1 * 16] = ex2(slot_exp(1));
+                    f[4 * 16] = ex2(-totI);
+                } else {
+                    f[2 * 16] = ex2(slot_exp(2));
+                    f[3 * 16] = ex2(slot_exp(3));
+                    f[5 * 16] = ex2(pre);
+                }
             }
             __syncwarp();
-            auto ldfac = [&](int slot, float (&v)[4]) {
-                const float4 t = *reinterpret_cast<const float4*>(fac + slot * 32 + 4 * cq);
-                v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+            auto ldfac = [&](int slot, float (&v)[2]) {
+                const float2 t = *reinterpret_cast<const float2*>(fac + slot * 16 + 2 * cq);
+                v[0] = t.x; v[1] = t.y;
             };
             ldfac(I, ebt);                      // 2^(total of the own sub-block)
             {                                   // K side: needed by the P^T MMAs
-                float ko[4][4];
+                float ko[4][2];
 #pragma unroll
                 for (int r = 0; r < 4; r++) {
-                    up4bf(kpk[r], ko[r]);
+                    up2bf(kpk[r], ko[r]);
 #pragma unroll
-                    for (int e = 0; e < 4; e++) ko[r][e] *= ei[r][e];
+                    for (int e = 0; e < 2; e++) ko[r][e] *= ei[r][e];
                 }
 #pragma unroll
                 for (int m = 0; m < 4; m++) {
                     if (m >= I) {               // target variant I' = m + 1 (I' = 4 -> Kend)
-                        float f[4], x4[4];
+                        float f[2], x4[2];
                         ldfac(m, f);
 #pragma unroll
                         for (int r = 0; r < 4; r++) {
-                            const int off = sw_chunk(rows[r], cchunk) + coff;
 #pragma unroll
-                            for (int e = 0; e < 4; e++) x4[e] = ko[r][e] * f[e];
+                            for (int e = 0; e < 2; e++) x4[e] = ko[r][e] * f[e];
                             // low-order halves only where the gw cancellation needs them: variant I' = I + 1 (and the own
                             // variant, phase 1); farther variants are damped by at least one whole sub-block of decay
-                            if (m == 3) st4bf(kend + off, x4);
-                            else if (m == I) st4bf_hilo(sm.kt + vbK[m + 1] + off, sm.kt_lo + vbK[m + 1] + off, x4);
-                            else st4bf(sm.kt + vbK[m + 1] + off, x4);
+                            if (m == 3) st2bf(kend + offs[r], x4);
+                            else if (m == I) st2bf_hilo(sm.kt + vbK[m + 1] + offs[r], sm.kt_lo + vbK[m + 1] + offs[r], x4);
+                            else st2bf(sm.kt + vbK[m + 1] + offs[r], x4);
                         }
                     }
                 }
@@ -470,34 +585,32 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 umma_commit(&sm.bar_mp);
             }
             __syncwarp();
-            if (tid == 0 && cb + 1 < nloc) issue_rkw(cb + 1);
+            if (tid == 0 && more) issue_rkw(nu);
             {                                   // R side: needed by the phase-2 MMAs only
-                float ro[4][4], fst[4];
+                float ro[4][2], fst[2];
                 ldfac(5, fst);
 #pragma unroll
                 for (int r = 0; r < 4; r++) {
-                    const int off = sw_chunk(rows[r], cchunk) + coff;
-                    float x4[4];
-                    up4bf(rpk[r], ro[r]);
+                    float x4[2];
+                    up2bf(rpk[r], ro[r]);
 #pragma unroll
-                    for (int e = 0; e < 4; e++) {
+                    for (int e = 0; e < 2; e++) {
                         ro[r][e] *= eo[r][e];
                         x4[e] = ro[r][e] * fst[e];
                     }
-                    st4bf_hilo(sm.rst + off, sm.rst_lo + off, x4);
+                    st2bf_hilo(sm.rst + offs[r], sm.rst_lo + offs[r], x4);
                 }
 #pragma unroll
                 for (int J = 0; J < 4; J++) {
                     if (J <= I) {
-                        float f[4], x4[4];
+                        float f[2], x4[2];
                         ldfac(J == I ? 4 : J, f);
 #pragma unroll
                         for (int r = 0; r < 4; r++) {
-                            const int off = sw_chunk(rows[r], cchunk) + coff;
 #pragma unroll
-                            for (int e = 0; e < 4; e++) x4[e] = ro[r][e] * f[e];
-                            if (J + 1 >= I) st4bf_hilo(sm.rp + vbR[J] + off, sm.rp_lo + vbR[J] + off, x4);   // own / previous sub-block
-                            else st4bf(sm.rp + vbR[J] + off, x4);
+                            for (int e = 0; e < 2; e++) x4[e] = ro[r][e] * f[e];
+                            if (J + 1 >= I) st2bf_hilo(sm.rp + vbR[J] + offs[r], sm.rp_lo + vbR[J] + offs[r], x4);   // own / previous sub-block
+                            else st2bf(sm.rp + vbR[J] + offs[r], x4);
                         }
                     }
                 }
@@ -512,18 +625,17 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         {
             // The causal mask is resolved per 16x16 block (warp-uniform: keep / zero / diagonal); the masked fragment goes
             // to the tiles with stmatrix (Q^T with the transposing form) instead of per-element stores.
-            float x[16];
-            uint32_t pk[8];
-            tmem_ld_16x32(tQ + lane_field + 32 * half, x);   // Q[p][q]: rows p (block qtr), columns q; keep q before p
-#pragma unroll
-            for (int cb = 0; cb < 2; cb++) {
-                const int cls = sgn * (qtr - (2 * half + cb));
+            float x[8];
+            uint32_t pk[4];
+            tmem_ld_16x16(tQ + lane_field + 16 * cqt, x);   // Q[p][q]: rows p (block qtr), columns q (block cqt); keep q before p
+            {
+                const int cls = sgn * (qtr - cqt);
                 if (cls > 0) {
 #pragma unroll
-                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = pack_bf16(x[8 * cb + 2 * i], x[8 * cb + 2 * i + 1]);
+                    for (int i = 0; i < 4; i++) pk[i] = pack_bf16(x[2 * i], x[2 * i + 1]);
                 } else if (cls < 0) {
 #pragma unroll
-                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = 0u;
+                    for (int i = 0; i < 4; i++) pk[i] = 0u;
                 } else {
 #pragma unroll
                     for (int rl = 0; rl < 2; rl++)
@@ -533,38 +645,33 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 #pragma unroll
                             for (int e = 0; e < 2; e++) {
                                 const int d = dfrag + sgn * (8 * hh - 8 * rl - e);   // sgn * (p - q)
-                                const float xv = x[4 * (2 * cb + rl) + 2 * hh + e];
+                                const float xv = x[4 * rl + 2 * hh + e];
                                 y[e] = d > 0 ? xv : 0.f;
                                 if (d == 0) sm.vg[frow + 8 * hh] = xv;
                             }
-                            pk[2 * (2 * cb + rl) + hh] = pack_bf16(y[0], y[1]);
+                            pk[2 * rl + hh] = pack_bf16(y[0], y[1]);
                         }
                 }
             }
-            {
-                const uint32_t qm_u32 = smem_u32(sm.qm), qmt_u32 = smem_u32(sm.qmt);
-                stsm_x4(qm_u32 + stoff[0], pk[0], pk[1], pk[2], pk[3]);
-                stsm_x4(qm_u32 + stoff[1], pk[4], pk[5], pk[6], pk[7]);
-                stsm_x4_trans(qmt_u32 + ttoff[0], pk[0], pk[1], pk[2], pk[3]);
-                stsm_x4_trans(qmt_u32 + ttoff[1], pk[4], pk[5], pk[6], pk[7]);
-            }
+            stsm_x4(smem_u32(sm.qm) + stoff, pk[0], pk[1], pk[2], pk[3]);
+            stsm_x4_trans(smem_u32(sm.qmt) + ttoff, pk[0], pk[1], pk[2], pk[3]);
             mbar_wait(&sm.bar_mp, par);
             WKV6_TS(64, 7);
             tc_fence_after();
-            tmem_ld_16x32(tP + lane_field + 32 * half, x);   // P^T[q][p]: rows q (block qtr), columns p; keep q before p
-#pragma unroll
-            for (int cb = 0; cb < 2; cb++) {
-                const int cls = sgn * ((2 * half + cb) - qtr);
+            tmem_ld_16x16(tP + lane_field + 16 * cqt, x);   // P^T[q][p]: rows q (block qtr), columns p (block cqt); keep q before p
+            {
+                const int cls = sgn * (cqt - qtr);
                 if (cls > 0) {
 #pragma unroll
-                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = pack_bf16(x[8 * cb + 2 * i], x[8 * cb + 2 * i + 1]);
+                    for (int i = 0; i < 4; i++) pk[i] = pack_bf16(x[2 * i], x[2 * i + 1]);
                 } else if (cls < 0) {
 #pragma unroll
-                    for (int i = 0; i < 4; i++) pk[4 * cb + i] = 0u;
+                    for (int i = 0; i < 4; i++) pk[i] = 0u;
                 } else {
                     float bon[2];
 #pragma unroll
-                    for (int hh = 0; hh < 2; hh++) bon[hh] = sm.bonus[0][frow + 8 * hh] + sm.bonus[1][frow + 8 * hh];
+                    for (int hh = 0; hh < 2; hh++)
+                        bon[hh] = (sm.bonus[0][frow + 8 * hh] + sm.bonus[1][frow + 8 * hh]) + (sm.bonus[2][frow + 8 * hh] + sm.bonus[3][frow + 8 * hh]);
 #pragma unroll
                     for (int rl = 0; rl < 2; rl++)
 #pragma unroll
@@ -573,17 +680,13 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
 #pragma unroll
                             for (int e = 0; e < 2; e++) {
                                 const int d = -dfrag + sgn * (8 * rl + e - 8 * hh);   // sgn * (p - q)
-                                y[e] = d > 0 ? x[4 * (2 * cb + rl) + 2 * hh + e] : (d == 0 ? bon[hh] : 0.f);
+                                y[e] = d > 0 ? x[4 * rl + 2 * hh + e] : (d == 0 ? bon[hh] : 0.f);
                             }
-                            pk[2 * (2 * cb + rl) + hh] = pack_bf16(y[0], y[1]);
+                            pk[2 * rl + hh] = pack_bf16(y[0], y[1]);
                         }
                 }
             }
-            {
-                const uint32_t pt_u32 = smem_u32(sm.pt);
-                stsm_x4(pt_u32 + stoff[0], pk[0], pk[1], pk[2], pk[3]);
-                stsm_x4(pt_u32 + stoff[1], pk[4], pk[5], pk[6], pk[7]);
-            }
+            stsm_x4(smem_u32(sm.pt) + stoff, pk[0], pk[1], pk[2], pk[3]);
         }
         fence_proxy_async();
         tc_fence_before();
@@ -648,53 +751,50 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                 t0j[m] = sm.blocktot[m][frow];
                 t1j[m] = sm.blocktot[m][frow + 8];
             }
-            // columns of this thread lie in row-blocks 2*half and 2*half+1 -> sub-blocks (direction order) iA, iB
-            const int rbA = 2 * half, rbB = 2 * half + 1;
-            const int iA = rev ? 3 - rbA : rbA, iB = rev ? 3 - rbB : rbB;
-            float sR[2][2], sK[2][2];   // [row hh][block A/B]: 2^(a_I) and 2^(A_L - a_{I+1})
+            // columns of this thread lie in row-block cqt -> sub-block (direction order) iA
+            const int iA = rev ? 3 - cqt : cqt;
+            float sR[2], sK[2];   // [row hh]: 2^(a_I) and 2^(A_L - a_{I+1})
 #pragma unroll
             for (int hh = 0; hh < 2; hh++) {
                 const float* tj = hh ? t1j : t0j;
-                float preA = 0.f, preB = 0.f, sufA = 0.f, sufB = 0.f;
+                float preA = 0.f, sufA = 0.f;
 #pragma unroll
                 for (int m = 0; m < 4; m++) {
                     if (m < iA) preA += tj[m];
-                    if (m < iB) preB += tj[m];
                     if (m > iA) sufA += tj[m];
-                    if (m > iB) sufB += tj[m];
                 }
-                sR[hh][0] = ex2(preA); sR[hh][1] = ex2(preB);
-                sK[hh][0] = ex2(sufA); sK[hh][1] = ex2(sufB);
+                sR[hh] = ex2(preA);
+                sK[hh] = ex2(sufA);
             }
-            float x[16], y[16];
-            tmem_ld_16x32(tR + lane_field + 32 * half, x);
-            tmem_ld_16x32(tRS + lane_field + 32 * half, y);
+            float x[8], y[8];
+            tmem_ld_16x16(tR + lane_field + 16 * cqt, x);
+            tmem_ld_16x16(tRS + lane_field + 16 * cqt, y);
 #pragma unroll
-            for (int rep = 0; rep < 4; rep++)
+            for (int rep = 0; rep < 2; rep++)
 #pragma unroll
                 for (int hh = 0; hh < 2; hh++)
 #pragma unroll
                     for (int e = 0; e < 2; e++) {
                         const int pp = fcol + 8 * rep + e, jj = frow + 8 * hh;
-                        xr[pp * XSTR + jj] = fmaf(sR[hh][rep >> 1], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
+                        xr[pp * XSTR + jj] = fmaf(sR[hh], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
                     }
-            tmem_ld_16x32(tK + lane_field + 32 * half, x);
-            tmem_ld_16x32(tKC + lane_field + 32 * half, y);
+            tmem_ld_16x16(tK + lane_field + 16 * cqt, x);
+            tmem_ld_16x16(tKC + lane_field + 16 * cqt, y);
 #pragma unroll
-            for (int rep = 0; rep < 4; rep++)
+            for (int rep = 0; rep < 2; rep++)
 #pragma unroll
                 for (int hh = 0; hh < 2; hh++)
 #pragma unroll
                     for (int e = 0; e < 2; e++) {
                         const int qq = fcol + 8 * rep + e, jj = frow + 8 * hh;
-                        xk[qq * XSTR + jj] = fmaf(sK[hh][rep >> 1], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
+                        xk[qq * XSTR + jj] = fmaf(sK[hh], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
                     }
             // gv tile [q][i]
             mbar_wait(&sm.bar_m2b, par);
             tc_fence_after();
-            tmem_ld_16x32(tGV + lane_field + 32 * half, x);
+            tmem_ld_16x16(tGV + lane_field + 16 * cqt, x);
 #pragma unroll
-            for (int rep = 0; rep < 4; rep++)
+            for (int rep = 0; rep < 2; rep++)
 #pragma unroll
                 for (int hh = 0; hh < 2; hh++) {
                     const int col = fcol + 8 * rep;
@@ -702,12 +802,12 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                         pack_bf16(x[4 * rep + 2 * hh], x[4 * rep + 2 * hh + 1]);
                 }
             // reverse state: C <- C 2^(A_L[j]) + dC;  then the anchor  hst[j] = sum_i S_0[i][j] C_0[i][j]
-            tmem_ld_16x32(tDC + lane_field + 32 * half, x);
+            tmem_ld_16x16(tDC + lane_field + 16 * cqt, x);
             const float f0 = ex2(t0j[0] + t0j[1] + t0j[2] + t0j[3]);
             const float f1 = ex2(t1j[0] + t1j[1] + t1j[2] + t1j[3]);
             float h0 = 0.f, h1 = 0.f;
 #pragma unroll
-            for (int rep = 0; rep < 4; rep++) {
+            for (int rep = 0; rep < 2; rep++) {
                 cs[4 * rep + 0] = fmaf(cs[4 * rep + 0], f0, x[4 * rep + 0]);
                 cs[4 * rep + 1] = fmaf(cs[4 * rep + 1], f0, x[4 * rep + 1]);
                 cs[4 * rep + 2] = fmaf(cs[4 * rep + 2], f1, x[4 * rep + 2]);
@@ -725,35 +825,34 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             h1 += __shfl_xor_sync(0xffffffffu, h1, 1);
             h1 += __shfl_xor_sync(0xffffffffu, h1, 2);
             if ((lane & 3) == 0) {
-                sm.hst[half][frow] = h0;
-                sm.hst[half][frow + 8] = h1;
+                sm.hst[cqt][frow] = h0;
+                sm.hst[cqt][frow + 8] = h1;
             }
             store_cp();
         }
         WKV6_TS(64, 12);
         __syncthreads();   // B4: xr / xk / hst / vg visible; all TMEM reads of this chunk done
         WKV6_TS(64, 13);
-        if (tid == 0 && cb + 1 < nloc) issue_sp(cb + 1);   // S_0 tile is dead after the anchor sum
+        if (tid == 0 && more) issue_sp(nu);   // S_0 tile is dead after the anchor sum
 
         // ================= final epilogue (row-major): gr, gk, gu, gw
         {
-            float dl[4][4], av[4][4];   // delta = k gkC - r grS,  a = r grS
-            const float4 hA = *reinterpret_cast<const float4*>(&sm.hst[0][c0]);
-            const float4 hB = *reinterpret_cast<const float4*>(&sm.hst[1][c0]);
-            const float hs[4] = {hA.x + hB.x, hA.y + hB.y, hA.z + hB.z, hA.w + hB.w};
+            float dl[4][2], av[4][2];   // delta = k gkC - r grS,  a = r grS
+            float hs[2];
+#pragma unroll
+            for (int e = 0; e < 2; e++) hs[e] = (sm.hst[0][c0 + e] + sm.hst[1][c0 + e]) + (sm.hst[2][c0 + e] + sm.hst[3][c0 + e]);
 #pragma unroll
             for (int r = 0; r < 4; r++) {
-                const int row = rows[r];
-                const int off = sw_chunk(row, cchunk) + coff;
-                float rr[4], kk[4], gr4[4], gk4[4];
-                up4bf(rpk[r], rr);
-                up4bf(kpk[r], kk);
+                const int row = row0 + sgn * r;
+                float rr[2], kk[2], gr4[2], gk4[2];
+                up2bf(rpk[r], rr);
+                up2bf(kpk[r], kk);
                 const float vg = sm.vg[row];
-                const float4 a4 = *reinterpret_cast<const float4*>(&xr[row * XSTR + c0]);
-                const float4 b4 = *reinterpret_cast<const float4*>(&xk[row * XSTR + c0]);
-                const float xa[4] = {a4.x, a4.y, a4.z, a4.w}, xb[4] = {b4.x, b4.y, b4.z, b4.w};
+                const float2 a4 = *reinterpret_cast<const float2*>(&xr[row * XSTR + c0]);
+                const float2 b4 = *reinterpret_cast<const float2*>(&xk[row * XSTR + c0]);
+                const float xa[2] = {a4.x, a4.y}, xb[2] = {b4.x, b4.y};
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
+                for (int e = 0; e < 2; e++) {
                     const float grS = eo[r][e] * xa[e];
                     const float gkC = ei[r][e] * ebt[e] * xb[e];
                     gr4[e] = fmaf(u4[e] * kk[e], vg, grS);
@@ -762,13 +861,13 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
                     av[r][e] = rr[e] * grS;
                     dl[r][e] = fmaf(kk[e], gkC, -av[r][e]);
                 }
-                st4bf(o_gr + off, gr4);
-                st4bf(o_gk + off, gk4);
+                st2bf(o_gr + offs[r], gr4);
+                st2bf(o_gk + offs[r], gk4);
             }
             // exclusive prefix of delta over the chunk in direction order: thread (4 rows) -> row groups -> sub-blocks
-            float pre[4][4];
+            float pre[4][2];
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
+            for (int e = 0; e < 2; e++) {
                 pre[0][e] = 0.f;
                 pre[1][e] = dl[0][e];
                 pre[2][e] = pre[1][e] + dl[1][e];
@@ -786,9 +885,9 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
             WKV6_TS(64, 14);
             __syncthreads();   // B5: dtot visible
-            float base[4];
+            float base[2];
 #pragma unroll
-            for (int e = 0; e < 4; e++) {
+            for (int e = 0; e < 2; e++) {
                 float s = hs[e];
 #pragma unroll
                 for (int m = 0; m < 4; m++)
@@ -797,19 +896,18 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
             }
 #pragma unroll
             for (int r = 0; r < 4; r++) {
-                const int row = rows[r];
-                const int t = t0 + row;
+                const int t = t0 + row0 + sgn * r;
                 // exact zeros the reference hard-codes (wkv6_cuda.cu:237,262): nothing precedes the direction's first
                 // step when S_0 = 0, nothing follows its last step when no gradient enters S_T
                 const bool first = !D.s0 && (rev ? t == T - 1 : t == 0);
                 const bool last = !D.gsT && (rev ? t == 0 : t == T - 1);
-                float gw4[4];
+                float gw4[2];
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
+                for (int e = 0; e < 2; e++) {
                     const float H = base[e] + pre[r][e] - av[r][e];
                     gw4[e] = (first || last) ? 0.f : -ew[r][e] * H;
                 }
-                st4bf(sm.o_gw + sw_chunk(row, cchunk) + coff, gw4);
+                st2bf(sm.o_gw + offs[r], gw4);
             }
         }
         fence_proxy_async();
@@ -817,42 +915,26 @@ __global__ void __launch_bounds__(256, 1) wkv6_bwd_chunk_kernel(const __grid_con
         WKV6_TS(64, 15);
         __syncthreads();   // B6: staging tiles complete; raw tiles and xr/xk no longer needed
         if (tid == 224) {
-            tma_store_3d(&D.mgr, o_gr, h * N, t0, b);
-            tma_store_3d(&D.mgk, o_gk, h * N, t0, b);
-            tma_store_3d(&D.mgv, o_gv, h * N, t0, b);
-            tma_store_3d(&D.mgw, sm.o_gw, h * N, t0, b);
+            tma_store_3d(&D.mgr, o_gr, cu.h * N, t0, cu.b);
+            tma_store_3d(&D.mgk, o_gk, cu.h * N, t0, cu.b);
+            tma_store_3d(&D.mgv, o_gv, cu.h * N, t0, cu.b);
+            tma_store_3d(&D.mgw, sm.o_gw, cu.h * N, t0, cu.b);
             tma_store_commit();
+        }
+        if (!more || nu.stage != cu.stage || nu.bh != cu.bh) {       // piece boundary (uniform)
+            piece_end(cu);
+            if (more) {
+                piece_start(nu);
+                tc_fence_before();
+                __syncthreads();         // the new piece's bf16 state tile is visible to the chunk-start MMAs
+                tc_fence_after();
+            }
         }
     }
 
     if (tid == 224) tma_store_wait<0>();
-    // gu[b][h*64 + c] = sum over rows of r k (v.gy): row groups by shuffle, sub-blocks through smem
-#pragma unroll
-    for (int e = 0; e < 4; e++) {
-        gu4[e] += __shfl_xor_sync(0xffffffffu, gu4[e], 8);
-        gu4[e] += __shfl_xor_sync(0xffffffffu, gu4[e], 16);
-    }
-    if (rg == 0) {
-#pragma unroll
-        for (int e = 0; e < 4; e++) sm.gured[warp][4 * cq + e] = gu4[e];
-    }
-    if (D.gs0 && seg == nseg - 1) {                      // the sweep reached the sequence's first step
-        float* g0 = D.gs0 + (size_t)bh * N * N;
-#pragma unroll
-        for (int rep = 0; rep < 4; rep++)
-#pragma unroll
-            for (int hh = 0; hh < 2; hh++)
-#pragma unroll
-                for (int e = 0; e < 2; e++) g0[(fcol + 8 * rep + e) * N + frow + 8 * hh] = cs[4 * rep + 2 * hh + e];
-    }
     tc_fence_before();
     __syncthreads();
-    if (tid < N) {
-        const int hc = tid >> 5, cc = tid & 31;
-        const float g = sm.gured[4 * hc + 0][cc] + sm.gured[4 * hc + 1][cc] + sm.gured[4 * hc + 2][cc] + sm.gured[4 * hc + 3][cc];
-        if (nseg > 1) p.seg_gu[((size_t)seq * nseg + seg) * N + tid] = g;      // summed by wkv6_bwd_seg_gu_kernel
-        else reinterpret_cast<__nv_bfloat16*>(D.gu)[(size_t)b * p.C + h * N + tid] = __float2bfloat16_rn(g);
-    }
     if (p.dbg && tid == 0 && blockIdx.x < 1024) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -1088,17 +1170,57 @@ static int pick_segments_bwd(const Params& p, size_t scratch_bytes, int* seg_chu
     return nseg;
 }
 
+// ---- balanced persistent grid (more sequences than SMs): see the schedule at the top of wkv6_bwd_chunk_kernel
+constexpr size_t kBalRecBytes = (size_t)N * N * 4 + 512;      // = kRecBytes of the kernel
+
+static int sm_count() {                                       // of the current device, cached per device
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    int n = cached[dev & 63].load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+        cached[dev & 63].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
+
+// CTAs per direction of a balanced launch (0: not applicable): the launch has more sequences than the GPU has SMs, i.e. the
+// one-CTA-per-sequence grid would run in two or more waves (one CTA is resident per SM) with an idle tail in the last one.
+static int pick_balanced(const Params& p) {
+    const int nsm = sm_count();
+    if (nsm <= 0 || p.ndir <= 0 || p.T <= 0) return 0;
+    const long long nseq = (long long)p.ndir * p.B * p.H;
+    const int ncta = nsm / p.ndir;
+    if (nseq <= nsm || ncta <= 0 || (long long)p.B * p.H < ncta) return 0;
+    const long long nch = (p.T + CL - 1) / CL;
+    if ((long long)p.B * p.H * nch * (nch > p.H ? nch : p.H) >= (1ll << 31)) return 0;   // exactness of the reciprocal divisions
+    if ((long long)p.B * p.H * nch * (ncta + 1) >= (1ll << 31)) return 0;               // 32-bit range arithmetic in the kernel
+    return ncta;
+}
+
+static size_t balanced_scratch_bytes(const Params& p) {
+    const int ncta = pick_balanced(p);
+    return ncta ? ((size_t)ncta * p.ndir + 1) * kBalRecBytes : 0;
+}
+
 size_t bwd_segment_scratch_bytes(const Params& p) {
     int sc = 0;
     const int nseg = pick_segments_bwd(p, ~(size_t)0, &sc);
-    return nseg ? (size_t)p.ndir * p.B * p.H * nseg * (N * N + 2 * N) * sizeof(float) : 0;
+    return nseg ? (size_t)p.ndir * p.B * p.H * nseg * (N * N + 2 * N) * sizeof(float) : balanced_scratch_bytes(p);
+}
+
+// reciprocals for the kernel's in-loop divisions: x / d = (x * magic) >> 31, exact while x * d < 2^31
+static void set_magics(Params& q) {
+    q.bal_magic_n = (unsigned)((1ull << 31) / (unsigned)((q.T + CL - 1) / CL)) + 1u;
+    q.bal_magic_h = (unsigned)((1ull << 31) / (unsigned)q.H) + 1u;
 }
 
 static int launch_bwd_main(const Params& q, int grid, cudaStream_t st) {
     const size_t smem = sizeof(BwdChunkSmem) + 1024;
     cudaError_t e = opt_in_smem_once(wkv6_bwd_chunk_kernel, smem, 1);
     if (e != cudaSuccess) return (int)e;
-    e = launch_pdl(wkv6_bwd_chunk_kernel, dim3(grid), dim3(256), smem, st, q);
+    e = launch_pdl(wkv6_bwd_chunk_kernel, dim3(grid), dim3(kBwdThreads), smem, st, q);
     count_launch(1);
     return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
@@ -1107,7 +1229,34 @@ int launch_bwd_chunk(const Params& p, cudaStream_t st) {
     Params q = p;
     q.dbg = debug_trace_buffer();
     q.nseg = 0;
+    q.bal_ncta = 0;
+    set_magics(q);
     return launch_bwd_main(q, q.ndir * q.B * q.H, st);
+}
+
+// -1: not applicable (or the scratch is missing / too small): the caller launches launch_bwd_chunk
+int launch_bwd_chunk_balanced(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    const int ncta = scratch ? pick_balanced(p) : 0;
+    if (ncta == 0 || scratch_bytes < balanced_scratch_bytes(p)) return -1;
+    // flags of the hand-over records carry the launch's epoch: 64 bits, never 0, different for every launch of the process
+    // (and from whatever the caller's scratch held before, up to a 2^-64 coincidence); consumed flags are reset to 0 by the
+    // kernel, which is what makes a CUDA-graph replay (same epoch every time) wait again
+    static std::atomic<unsigned long long> counter{0};
+    static const unsigned long long salt = [] {
+        unsigned long long x = (unsigned long long)std::chrono::steady_clock::now().time_since_epoch().count();
+        x ^= (unsigned long long)(uintptr_t)&counter * 0x9E3779B97F4A7C15ull;
+        x ^= x >> 29; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 32;
+        return x | 1ull;
+    }();
+    Params q = p;
+    q.dbg = debug_trace_buffer();
+    q.nseg = 0;
+    q.bal_ncta = ncta;
+    set_magics(q);
+    q.bal_rec = static_cast<unsigned char*>(scratch);
+    q.bal_epoch = (salt << 32) ^ (salt >> 32) ^ ((counter.fetch_add(1, std::memory_order_relaxed) + 1) * 0x9E3779B97F4A7C15ull);
+    if (q.bal_epoch == 0) q.bal_epoch = 1;
+    return launch_bwd_main(q, ncta * q.ndir, st);
 }
 
 // -1: the shape is not segmented (or the scratch is missing / too small): the caller launches launch_bwd_chunk
@@ -1119,6 +1268,8 @@ int launch_bwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_by
     q.dbg = debug_trace_buffer();
     const int nseq = q.ndir * q.B * q.H;
     q.nseg = nseg;
+    q.bal_ncta = 0;
+    set_magics(q);
     q.seg_chunks = sc;
     q.seg_state = static_cast<float*>(scratch);
     q.seg_decay = q.seg_state + (size_t)nseq * nseg * N * N;

@@ -43,6 +43,11 @@ struct Params {
     float* seg_gu;                        // time-segmented backward: [ndir][B*H][nseg][64] partial gu of every segment
     int corr_first;                       // one-pass segmented forward: first chunk wkv6_fwd_corr_kernel touches
     float* seg_prefix;                    // one-pass segmented forward: [ndir][B*H][chunks][64] decay from segment start to chunk start
+    // balanced persistent backward (wkv6_chunk_bwd.cu): CTAs per direction (0: off), hand-over records, flag value of the launch
+    int bal_ncta;
+    unsigned bal_magic_n, bal_magic_h;    // 2^31 / chunks-per-sequence + 1, 2^31 / H + 1 (every chunk-backward launch)
+    unsigned char* bal_rec;
+    unsigned long long bal_epoch;
     unsigned long long* dbg;              // optional clock64() trace of one CTA (wkv6_b200_debug_trace), else null
 };
 
@@ -59,6 +64,7 @@ int launch_fwd_scan_segmented(int dtype, const Params& p, void* scratch, size_t 
 int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
 int launch_bwd_chunk(const Params& p, cudaStream_t st);   // bf16 only, tcgen05; needs DirArgs::ckpt
 int launch_bwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);   // -1: not applicable
+int launch_bwd_chunk_balanced(const Params& p, void* scratch, size_t scratch_bytes, cudaStream_t st);    // -1: not applicable
 size_t bwd_segment_scratch_bytes(const Params& p);
 int launch_tmix_mix_bwd(int dtype, int B, int T, int C, const void* x, const void* m, const void* const* maa, const void* const* g,
                         int reverse, void* gx, void* gm, float* gmaa, cudaStream_t st);

@@ -113,4 +113,28 @@ __device__ __forceinline__ void st4bf_hilo(uint8_t* hi, uint8_t* lo, const float
     *reinterpret_cast<uint2*>(lo) = make_uint2(pack_bf16(l0, l1), pack_bf16(l2, l3));
 }
 
+
+// 16 TMEM lanes x 16 columns -> 8 registers per thread (same register map as tmem_ld_16x32 with rep = 0, 1)
+__device__ __forceinline__ void tmem_ld_16x16(uint32_t taddr, float (&v)[8]) {
+    uint32_t u[8];
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 8; i++) v[i] = __uint_as_float(u[i]);
+}
+
+// two-channel forms of the helpers above (one 32-bit word = 2 consecutive bf16)
+__device__ __forceinline__ void up2bf(const uint32_t q, float (&f)[2]) {
+    f[0] = __uint_as_float(q << 16);
+    f[1] = __uint_as_float(q & 0xffff0000u);
+}
+__device__ __forceinline__ void st2bf(uint8_t* p, const float (&f)[2]) { *reinterpret_cast<uint32_t*>(p) = pack_bf16(f[0], f[1]); }
+__device__ __forceinline__ void st2bf_hilo(uint8_t* hi, uint8_t* lo, const float (&f)[2]) {
+    const uint32_t h0 = pack_bf16(f[0], f[1]);
+    *reinterpret_cast<uint32_t*>(hi) = h0;
+    *reinterpret_cast<uint32_t*>(lo) = pack_bf16(f[0] - __uint_as_float(h0 << 16), f[1] - __uint_as_float(h0 & 0xffff0000u));
+}
+
 }  // namespace wkv6

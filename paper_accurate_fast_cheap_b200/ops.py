@@ -55,6 +55,16 @@ def set_segmentation(enabled: bool) -> None:
     _segmentation = bool(enabled)
 
 
+_balanced = True
+
+
+def set_balanced(enabled: bool) -> None:
+    """Test / A-B switch: with False the chunk backward of more sequences than SMs gets no scratch and runs one CTA per
+    sequence instead of the balanced persistent grid (hand-over records in the scratch)."""
+    global _balanced
+    _balanced = bool(enabled)
+
+
 def _scratch(t: torch.Tensor, ndir: int):
     """Scratch for the time-segmented forward of few, long sequences (include/wkv6_b200.h): allocated per call from the
     caching allocator -- stream-ordered, so concurrent forwards on different streams never share a buffer -- and only for
@@ -101,10 +111,14 @@ def wkv6_forward_raw(r, k, v, w, u, s0=None, reverse=False, want_state=False, ck
 
 def _bwd_workspace_bytes(L, r, B, T, C, H, ndir, ckpt) -> int:
     """Without checkpoints: everything the backward needs.  With checkpoints: only the scratch of the time-segmented sweep
-    (0 unless the launch is few, long sequences; `set_segmentation(False)` turns it off)."""
+    (few, long sequences; `set_segmentation(False)` turns it off) or of the balanced persistent grid (more sequences than
+    SMs; `set_balanced(False)`); 0 for every other shape."""
+    few_long = ndir * B * H <= 74        # the time-segmented sweep (else: the balanced persistent grid, more sequences than SMs)
+    want_scratch = (_segmentation and T >= 2048) if few_long else _balanced
     if ckpt is None:
-        return L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, ndir)
-    if not _segmentation or T < 2048:
+        nb = L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, ndir)
+        return nb if want_scratch else nb - L.wkv6_b200_backward_scratch_bytes(_dtype_code(r), B, T, C, H, ndir)
+    if not want_scratch:
         return 0
     return L.wkv6_b200_backward_scratch_bytes(_dtype_code(r), B, T, C, H, ndir)
 

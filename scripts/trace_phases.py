@@ -28,6 +28,7 @@ for name, base, n in (("fwd", 0, 15), ("bwd", 64, 16)):
         ts = v[base + off: base + off + n]
         t0 = ts[0]
         print(name, who, " ".join(f"{i}:{(x - t0) if x else -1}" for i, x in enumerate(ts)))
+print("bwd loop tops of CTA 0 (cycles per chunk):", " ".join(str(v[96 + i + 1] - v[96 + i]) for i in range(31) if v[96 + i + 1] and v[96 + i]))
 L.wkv6_b200_debug_trace(0, None)
 
 # ---- per-CTA timeline of the forward chunk kernel (globaltimer ns): residency per SM, wave structure
