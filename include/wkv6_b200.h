@@ -120,7 +120,13 @@ size_t wkv6_b200_backward_workspace_bytes(int dtype, int B, int T, int C, int H,
  * IS given checkpoints sweeps every sequence in 2..40 time segments over all SMs (four launches: segment-local reverse
  * states, segment scan, gradients, gu reduction); same results to the dtype's tolerance.  Returns 0 for shapes that would
  * not be segmented; wkv6_b200_backward_workspace_bytes() includes these bytes.  The reference cannot run these shapes at
- * all: its backward indexes a ctx_len-sized array (wkv6_cuda.cu:207). */
+ * all: its backward indexes a ctx_len-sized array (wkv6_cuda.cu:207).
+ * The same bytes serve the opposite case, MORE sequences than SMs (directions * B * H > SM count: the training batch):
+ * given them, the backward runs a balanced persistent grid -- one CTA per SM, every direction's (sequence, 64-step chunk)
+ * units cut into equal ranges, a sequence that is cut between two CTAs hands its reverse state and partial gu over through
+ * a 16.5 KB record in this scratch ((CTAs + 1) records, 2.5 MB on a B200) -- instead of one CTA per sequence in several
+ * waves.  One launch either way; contents of the scratch on entry are arbitrary, calls that overlap on the GPU must not
+ * share it.  Gradients are those of the one-CTA-per-sequence launch bit for bit, except gu (its partial sums regroup). */
 size_t wkv6_b200_backward_scratch_bytes(int dtype, int B, int T, int C, int H, int ndirections);
 
 int wkv6_b200_backward(int dtype, int B, int T, int C, int H,

@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
         mbar_init(&sm.bar_vg[1], 1);
         mbar_init(&sm.bar_sp, 1);
         mbar_init(&sm.bar_mp, 4);     // MMA groups are issued by several warps' lane 0 in parallel (an issue costs
-        mbar_init(&sm.bar_m1, 3);     // ~50 cycles of dependent uniform-datapath work); every issuer commits
+        mbar_init(&sm.bar_m1, 1);     // ~50 cycles of dependent uniform-datapath work); every issuer commits (bar_m1: Q, warp 0)
         mbar_init(&sm.bar_m2, 4);       // R^T / K^T groups: four issuing lanes
         mbar_init(&sm.bar_m2b, 2);      // GV, dC
         fence_barrier_init();
@@ -380,22 +380,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
         // CTA-wide barrier).  The store thread is warp 7 lane 0: it issues no MMAs, so this wait delays nobody.
         if (tid == 224) tma_store_wait_read<0>();
         if (tid == 0 && more) issue_vg(nu, (cb + 1) & 1);   // other V / G buffer: its readers finished last iteration
-        if (warp < 3 && elect_one()) {
-            // ---- MMA phase 1a: everything that needs no preprocessing (V, G, S_0, C are raw / carried tiles)
+        if (warp == 0 && elect_one()) {
+            // ---- MMA phase 1a: Q needs no preprocessing (V, G are raw tiles).  Issue only: a tcgen05.commit right behind the
+            // MMAs parks the issuing thread until the tensor pipe has drained them (measured: 430 cycles for this group, by which
+            // the issuing warps reached barrier B1 late); the commit follows after the R-side preprocessing, when it is free.
             mbar_wait(&sm.bar_vg[cb & 1], (cb >> 1) & 1);
-            mbar_wait(&sm.bar_sp, par);
             tc_fence_after();
-            if (warp == 0) {
 #pragma unroll
-                for (int ks = 0; ks < 4; ks++) umma(tQ, dk_g + DOFF(ks * 32), dk_v + DOFF(ks * 32), ID_KK64, ks > 0);
-            } else if (warp == 1) {
-#pragma unroll
-                for (int ks = 0; ks < 4; ks++) umma(tRS, dk_sp + DOFF(ks * 32), dk_g + DOFF(ks * 32), ID_KK64, ks > 0);
-            } else {
-#pragma unroll
-                for (int ks = 0; ks < 4; ks++) umma(tKC, dk_cp + DOFF(ks * 32), dk_v + DOFF(ks * 32), ID_KK64, ks > 0);
-            }
-            umma_commit(&sm.bar_m1);
+            for (int ks = 0; ks < 4; ks++) umma(tQ, dk_g + DOFF(ks * 32), dk_v + DOFF(ks * 32), ID_KK64, ks > 0);
         }
         __syncwarp();
 
@@ -582,7 +574,17 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++)
                     umma(tP + rowlo, dk_kt + DOFF(vbi + ks * 32), dk_roff + DOFF(rowlo * 128 + ks * 32), ID_KK16, ks > 0);
-                umma_commit(&sm.bar_mp);
+                // RS^T = S_0^T G^T and KC^T = C^T V^T (raw / carried tiles) are read by E2 only: they queue up behind P^T and are
+                // covered by their issuers' phase-2 commits (a commit tracks every earlier MMA of its thread)
+                if (warp == 1) {
+                    mbar_wait(&sm.bar_sp, par);
+                    tc_fence_after();
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++) umma(tRS, dk_sp + DOFF(ks * 32), dk_g + DOFF(ks * 32), ID_KK64, ks > 0);
+                } else if (warp == 2) {
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++) umma(tKC, dk_cp + DOFF(ks * 32), dk_v + DOFF(ks * 32), ID_KK64, ks > 0);
+                }
             }
             __syncwarp();
             if (tid == 0 && more) issue_rkw(nu);
@@ -617,6 +619,11 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
             }
         }
 
+        if (warp < 4 && elect_one()) {            // (the same lanes that issued)
+            umma_commit(&sm.bar_mp);
+            if (warp == 0) umma_commit(&sm.bar_m1);
+        }
+        __syncwarp();
         WKV6_TS(64, 5);
         // ================= E1: Q -> masked Q, Q^T, vg;  P^T -> masked P^T with the bonus diagonal
         mbar_wait(&sm.bar_m1, par);
