@@ -5,7 +5,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libwkv6_b200.so")
+# WKV6_B200_LIB: another build of the same sources (the phase-trace build of build.py --trace, A/B variants of a kernel)
+LIB_PATH = os.environ.get("WKV6_B200_LIB") or os.path.join(_HERE, "libwkv6_b200.so")
 TORCH_LIB_PATH = os.path.join(_HERE, "libwkv6_b200_torch.so")
 
 DTYPE_BF16, DTYPE_F32 = 0, 1

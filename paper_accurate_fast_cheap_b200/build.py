@@ -9,6 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libwkv6_b200.so")
+TRACE_LIB = os.path.join(HERE, "libwkv6_b200_trace.so")   # -DWKV6_TRACE_PHASES=1; loaded when WKV6_B200_LIB points at it
 TORCH_LIB = os.path.join(HERE, "libwkv6_b200_torch.so")
 CUDA_SOURCES = ["wkv6_scan.cu", "wkv6_chunk_lean.cu", "wkv6_chunk_bwd.cu", "wkv6_tmix.cu", "convmod.cu", "wkv6_capi.cu"]
 HEADERS = ["wkv6_common.cuh", "wkv6_scan.cuh", "wkv6_umma.cuh", "wkv6_fwd_tiles.cuh", "../../include/wkv6_b200.h"]
@@ -30,16 +31,19 @@ def _nvcc() -> str:
     return "nvcc"
 
 
-def build_cuda(force: bool = False, verbose: bool = False) -> str:
+def build_cuda(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """trace=True builds libwkv6_b200_trace.so: the same sources with the in-loop clock64() phase stamps of the chunk kernels
+    compiled in (scripts/trace_phases.py loads it through WKV6_B200_LIB); the shipped library is built without them."""
     deps = [os.path.join(CSRC, s) for s in CUDA_SOURCES + HEADERS]
-    if not force and _newer(LIB, deps):
-        return LIB
+    lib = TRACE_LIB if trace else LIB          # the trace build is a file of its own: it never replaces the shipped library
+    if not force and _newer(lib, deps):
+        return lib
     objs = []
     procs = []
     for s in CUDA_SOURCES:
-        o = os.path.join(CSRC, s.replace(".cu", ".o"))
+        o = os.path.join(CSRC, s.replace(".cu", "_trace.o" if trace else ".o"))
         objs.append(o)
-        cmd = [_nvcc()] + NVCC_FLAGS + ["-c", os.path.join(CSRC, s), "-o", o]
+        cmd = [_nvcc()] + NVCC_FLAGS + (["-DWKV6_TRACE_PHASES=1"] if trace else []) + ["-c", os.path.join(CSRC, s), "-o", o]
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     log = []
     for s, pr in procs:
@@ -47,13 +51,14 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
         log.append(f"==== {s}\n{out}")
         if pr.returncode != 0:
             raise RuntimeError(f"nvcc failed on {s}:\n{out}")
-    with open(os.path.join(CSRC, "ptxas_v.log"), "w") as f:
-        f.write("\n".join(log))
+    if not trace:
+        with open(os.path.join(CSRC, "ptxas_v.log"), "w") as f:
+            f.write("\n".join(log))
     if verbose:
         print("\n".join(log))
-    cmd = [_nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
+    cmd = [_nvcc(), "-shared", "-o", lib] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"]
     subprocess.run(cmd, check=True)
-    return LIB
+    return lib
 
 
 def build_torch_shim(force: bool = False) -> str:
@@ -76,10 +81,12 @@ def build_torch_shim(force: bool = False) -> str:
     return TORCH_LIB
 
 
-def build_all(force: bool = False, verbose: bool = False):
+def build_all(force: bool = False, verbose: bool = False, trace: bool = False):
+    if trace:
+        return build_cuda(force, verbose, True), None
     return build_cuda(force, verbose), build_torch_shim(force)
 
 
 if __name__ == "__main__":
-    build_all(force="--force" in sys.argv, verbose=True)
+    build_all(force="--force" in sys.argv, verbose=True, trace="--trace" in sys.argv)
     print("built", LIB, TORCH_LIB)

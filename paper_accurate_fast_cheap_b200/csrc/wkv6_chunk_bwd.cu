@@ -232,6 +232,24 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
     const int c0 = 16 * ch + 2 * cq;
     const int coff = (c0 & 7) * 2, cchunk = c0 >> 3;
     const int row0 = rev ? 63 - (16 * I + 4 * rg) : 16 * I + 4 * rg;   // the thread's rows: row0 + sgn * r, r = 0..3
+    // Loop-invariant shared-memory offsets.  offs: the thread's four (row, channel pair) words of a row-major tile;
+    // fo[2 * rep + hh]: word (row frow + 8 hh, columns fcol + 8 rep ..+1) of a fragment-layout tile; xbase: its fp32
+    // transposition-buffer slot.  (ptxas rematerialises some of this swizzle arithmetic inside the chunk loop instead of
+    // keeping it in registers; pinning the values with empty asm statements was measured 1.2 % SLOWER.)
+    int offs[4];
+    uint32_t fo[4];
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+        offs[r] = sw_chunk(row0 + sgn * r, cchunk) + coff;
+    }
+#pragma unroll
+    for (int rep = 0; rep < 2; rep++)
+#pragma unroll
+        for (int hh = 0; hh < 2; hh++) {
+            const int col = fcol + 8 * rep;
+            fo[2 * rep + hh] = (uint32_t)(sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2);
+        }
+    const int xbase = fcol * XSTR + frow;
     const int vbK_own = I == 0 ? vbK[0] : I == 1 ? vbK[1] : I == 2 ? vbK[2] : vbK[3];
 
     pdl_wait();   // first global access below (see wkv6_common.cuh)
@@ -243,11 +261,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
 #pragma unroll
         for (int rep = 0; rep < 2; rep++)
 #pragma unroll
-            for (int hh = 0; hh < 2; hh++) {
-                const int col = fcol + 8 * rep;
-                *reinterpret_cast<uint32_t*>(sm.cp + sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2) =
-                    pack_bf16(cs[4 * rep + 2 * hh], cs[4 * rep + 2 * hh + 1]);
-            }
+            for (int hh = 0; hh < 2; hh++)
+                *reinterpret_cast<uint32_t*>(sm.cp + fo[2 * rep + hh]) = pack_bf16(cs[4 * rep + 2 * hh], cs[4 * rep + 2 * hh + 1]);
     };
     // start of a piece: the reverse state (gradient into S_T / what the segment scan left in the slot / the record the
     // previous CTA handed over), u of the head, gu = 0, bf16 copy of the state for the first chunk's MMAs
@@ -378,20 +393,26 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
     constexpr uint32_t ID_MM64 = umma_idesc(1, 1, 64, 64);
 
     for (int cb = 0; cb < nunits; cb++) {
-        const Unit cu = unit_at(cb);
         const bool more = cb + 1 < nunits;
-        const Unit nu = unit_at(cb + 1);                 // the chunk after this one (if `more`)
-        const int t0 = tile_q(cu) * CL;                  // first step of the chunk's tile in memory
+        // what every warp needs of the schedule: the chunk's position in its sequence and whether its piece ends here; the
+        // full units (batch row, head: two more reciprocal divisions each) are computed where they are used -- by the lanes
+        // that issue TMA and at the piece boundaries
+        const int xw = cb - lenA;                        // position in the run of whole sequences
+        const int c_cur = xw < 0 ? cb : xw < lenW ? xw - udiv(xw, p.bal_magic_n) * nchunks : cB0 + (xw - lenW);
+        const bool pend = !more || cb + 1 == lenA || (xw >= 0 && xw < lenW && c_cur == nchunks - 1);   // (uniform)
+        const int t0 = (rev ? c_cur : nchunks - 1 - c_cur) * CL;   // first step of the chunk's tile in memory
         const uint32_t par = cb & 1;
         const uint64_t vgoff = (cb & 1) ? DOFF(CL * 128) : 0;   // V / G buffer of this chunk (v[1] - v[0] = g[1] - g[0] = 8 KB)
         const uint64_t dk_g = dk_g0 + vgoff, dk_v = dk_v0 + vgoff, dm_g = dm_g0 + vgoff;
         const int c_ts = cb;
+#if WKV6_TRACE_PHASES
         if (wkv6_trace_on && tid == 0 && cb < 32) p.dbg[96 + cb] = clock64();   // loop-top stamp of every chunk (debug trace)
+#endif
         WKV6_TS(64, 0);
         // staging tiles of the previous chunk have been read (they alias operand tiles that are rewritten after the next
         // CTA-wide barrier).  The store thread is warp 7 lane 0: it issues no MMAs, so this wait delays nobody.
         if (tid == 224) tma_store_wait_read<0>();
-        if (tid == 0 && more) issue_vg(nu, (cb + 1) & 1);   // other V / G buffer: its readers finished last iteration
+        if (tid == 0 && more) issue_vg(unit_at(cb + 1), (cb + 1) & 1);   // other V / G buffer: its readers finished last iteration
         if (warp == 0 && elect_one()) {
             // ---- MMA phase 1a: Q needs no preprocessing (V, G are raw tiles).  Issue only: a tcgen05.commit right behind the
             // MMAs parks the issuing thread until the tensor pipe has drained them (measured: 430 cycles for this group, by which
@@ -408,23 +429,19 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
         WKV6_TS(64, 1);
         float eo[4][2], ei[4][2], ew[4][2], ebt[2];           // ebt = 2^(log2 decay total of the own sub-block)
         uint32_t rpk[4], kpk[4];                         // this thread's r and k (bf16 x2 per row) for the later phases
-        int offs[4];                                     // byte offsets of the thread's four (row, channel pair) words in a tile
         {
             float rr[4][2], kk[4][2], l2[4][2], dstep[4][2], bsum[4];
             float xmax = 0.f;
 #pragma unroll
             for (int r = 0; r < 4; r++) {
-                const int pos = 16 * I + 4 * rg + r;
-                const int row = rev ? 63 - pos : pos;
-                const int off = sw_chunk(row, cchunk) + coff;
-                offs[r] = off;
+                const int row = row0 + sgn * r;
+                const int off = offs[r];
                 float w4[2];
                 rpk[r] = *reinterpret_cast<const uint32_t*>(sm.raw_r + off);
                 kpk[r] = *reinterpret_cast<const uint32_t*>(sm.raw_k + off);
                 up2bf(rpk[r], rr[r]);
                 up2bf(kpk[r], kk[r]);
                 up2bf(*reinterpret_cast<const uint32_t*>(sm.raw_w + off), w4);
-                const bool valid = t0 + row < T;
                 float bs = 0.f;
 #pragma unroll
                 for (int e = 0; e < 2; e++) {
@@ -432,12 +449,19 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
                     const float x = ex2(w4[e] * kLog2e);            // exp(w)
                     ew[r][e] = x;
                     xmax = fmaxf(xmax, x);
-                    const float l = fmaxf(-x * kLog2e, -kClampL2);
-                    l2[r][e] = valid ? l : 0.f;
-                    dstep[r][e] = ex2(l2[r][e]);                    // the step's decay
+                    l2[r][e] = fmaxf(-x * kLog2e, -kClampL2);
                 }
                 bsum[r] = bs;
             }
+            if (t0 + CL > T) {        // ragged last tile of the sequence (uniform): steps at or beyond T do not decay
+#pragma unroll
+                for (int r = 0; r < 4; r++)
+                    if (t0 + row0 + sgn * r >= T) l2[r][0] = l2[r][1] = 0.f;
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) dstep[r][e] = ex2(l2[r][e]);   // the step's decay
             // d l / d w where the decay floor is active (exp(w) > 5; never with trained decays, so the whole warp skips it):
             // the recurrence ran with 2^l instead of 2^lt, so the H_p computed below is (floored decay) x dL/d(decay); the
             // true step has (true decay) x the same derivative to first order: rescale exp(w) by 2^(lt - l)
@@ -599,7 +623,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
                 }
             }
             __syncwarp();
-            if (tid == 0 && more) issue_rkw(nu);
+            if (tid == 0 && more) issue_rkw(unit_at(cb + 1));
             {                                   // R side: needed by the phase-2 MMAs only
                 float ro[4][2], fst[2];
                 ldfac(5, fst);
@@ -797,8 +821,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
                 for (int hh = 0; hh < 2; hh++)
 #pragma unroll
                     for (int e = 0; e < 2; e++) {
-                        const int pp = fcol + 8 * rep + e, jj = frow + 8 * hh;
-                        xr[pp * XSTR + jj] = fmaf(sR[hh], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
+                        xr[xbase + (8 * rep + e) * XSTR + 8 * hh] = fmaf(sR[hh], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
                     }
             tmem_ld_16x16(tK + lane_field + 16 * cqt, x);
             tmem_ld_16x16(tKC + lane_field + 16 * cqt, y);
@@ -808,8 +831,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
                 for (int hh = 0; hh < 2; hh++)
 #pragma unroll
                     for (int e = 0; e < 2; e++) {
-                        const int qq = fcol + 8 * rep + e, jj = frow + 8 * hh;
-                        xk[qq * XSTR + jj] = fmaf(sK[hh], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
+                        xk[xbase + (8 * rep + e) * XSTR + 8 * hh] = fmaf(sK[hh], y[4 * rep + 2 * hh + e], x[4 * rep + 2 * hh + e]);
                     }
             // gv tile [q][i]
             mbar_wait(&sm.bar_m2b, par);
@@ -818,11 +840,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
 #pragma unroll
             for (int rep = 0; rep < 2; rep++)
 #pragma unroll
-                for (int hh = 0; hh < 2; hh++) {
-                    const int col = fcol + 8 * rep;
-                    *reinterpret_cast<uint32_t*>(o_gv + sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2) =
-                        pack_bf16(x[4 * rep + 2 * hh], x[4 * rep + 2 * hh + 1]);
-                }
+                for (int hh = 0; hh < 2; hh++)
+                    *reinterpret_cast<uint32_t*>(o_gv + fo[2 * rep + hh]) = pack_bf16(x[4 * rep + 2 * hh], x[4 * rep + 2 * hh + 1]);
             // reverse state: C <- C 2^(A_L[j]) + dC;  then the anchor  hst[j] = sum_i S_0[i][j] C_0[i][j]
             tmem_ld_16x16(tDC + lane_field + 16 * cqt, x);
             const float f0 = ex2(t0j[0] + t0j[1] + t0j[2] + t0j[3]);
@@ -834,9 +853,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
                 cs[4 * rep + 1] = fmaf(cs[4 * rep + 1], f0, x[4 * rep + 1]);
                 cs[4 * rep + 2] = fmaf(cs[4 * rep + 2], f1, x[4 * rep + 2]);
                 cs[4 * rep + 3] = fmaf(cs[4 * rep + 3], f1, x[4 * rep + 3]);
-                const int col = fcol + 8 * rep;
-                const uint32_t s0w = *reinterpret_cast<const uint32_t*>(sm.sp + sw_chunk(frow, col >> 3) + (col & 7) * 2);
-                const uint32_t s1w = *reinterpret_cast<const uint32_t*>(sm.sp + sw_chunk(frow + 8, col >> 3) + (col & 7) * 2);
+                const uint32_t s0w = *reinterpret_cast<const uint32_t*>(sm.sp + fo[2 * rep]);
+                const uint32_t s1w = *reinterpret_cast<const uint32_t*>(sm.sp + fo[2 * rep + 1]);
                 h0 = fmaf(__uint_as_float(s0w << 16), cs[4 * rep + 0], h0);
                 h0 = fmaf(__uint_as_float(s0w & 0xffff0000u), cs[4 * rep + 1], h0);
                 h1 = fmaf(__uint_as_float(s1w << 16), cs[4 * rep + 2], h1);
@@ -855,7 +873,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
         WKV6_TS(64, 12);
         __syncthreads();   // B4: xr / xk / hst / vg visible; all TMEM reads of this chunk done
         WKV6_TS(64, 13);
-        if (tid == 0 && more) issue_sp(nu);   // S_0 tile is dead after the anchor sum
+        if (tid == 0 && more) issue_sp(unit_at(cb + 1));   // S_0 tile is dead after the anchor sum
 
         // ================= final epilogue (row-major): gr, gk, gu, gw
         {
@@ -937,16 +955,17 @@ __global__ void __launch_bounds__(kBwdThreads, 1) wkv6_bwd_chunk_kernel(const __
         WKV6_TS(64, 15);
         __syncthreads();   // B6: staging tiles complete; raw tiles and xr/xk no longer needed
         if (tid == 224) {
+            const Unit cu = unit_at(cb);
             tma_store_3d(&D.mgr, o_gr, cu.h * N, t0, cu.b);
             tma_store_3d(&D.mgk, o_gk, cu.h * N, t0, cu.b);
             tma_store_3d(&D.mgv, o_gv, cu.h * N, t0, cu.b);
             tma_store_3d(&D.mgw, sm.o_gw, cu.h * N, t0, cu.b);
             tma_store_commit();
         }
-        if (!more || nu.stage != cu.stage || nu.bh != cu.bh) {       // piece boundary (uniform)
-            piece_end(cu);
+        if (pend) {                      // piece boundary
+            piece_end(unit_at(cb));
             if (more) {
-                piece_start(nu);
+                piece_start(unit_at(cb + 1));
                 tc_fence_before();
                 __syncthreads();         // the new piece's bf16 state tile is visible to the chunk-start MMAs
                 tc_fence_after();

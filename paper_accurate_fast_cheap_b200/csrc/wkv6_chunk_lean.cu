@@ -363,7 +363,9 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
         const bool more = c + 1 < nchunks;
         const int c_ts = c;
         WKV6_TS(0, 0);
+#if WKV6_TRACE_PHASES
         if (p.dbg && blockIdx.x == 0 && tid == 0 && c < 32) p.dbg[32 + c] = clock64();   // loop-top stamp of every chunk
+#endif
 
         // ---------------- P^T readout: causal mask + bonus diagonal -> bf16 tile (MN-major A of G2)
         if (!so) {

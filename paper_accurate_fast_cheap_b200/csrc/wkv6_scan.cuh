@@ -82,10 +82,20 @@ unsigned long long* debug_trace_buffer();
 // needs `const bool wkv6_trace_on = WKV6_TRACE_ON(p, tid);` in scope (one predicate per thread instead of five tests per
 // stamp: the stamps were 3.7 % of the executed instructions of the forward kernel)
 #define WKV6_TRACE_ON(p, tid) ((p).dbg != nullptr && blockIdx.x == 0 && ((tid) == 0 || (tid) == 32))
+// The in-loop phase stamps are compiled in only with -DWKV6_TRACE_PHASES=1 (python -m paper_accurate_fast_cheap_b200.build
+// --trace; scripts/trace_phases.py asks for it): 17 predicated branches per chunk were 3 % of the backward kernel's
+// instructions.  The per-CTA start / end stamps (outside the chunk loops) are always there.
+#ifndef WKV6_TRACE_PHASES
+#define WKV6_TRACE_PHASES 0
+#endif
+#if WKV6_TRACE_PHASES
 #define WKV6_TS(base, i)                                                                          \
     do {                                                                                          \
         if (wkv6_trace_on && c_ts == WKV6_TS_CHUNK) p.dbg[(base) + (tid ? 16 : 0) + (i)] = clock64(); \
     } while (0)
+#else
+#define WKV6_TS(base, i) do { (void)wkv6_trace_on; (void)c_ts; } while (0)
+#endif
 
 
 // Launch with the programmatic-stream-serialization attribute (see pdl_wait() in wkv6_common.cuh).

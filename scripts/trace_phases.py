@@ -1,6 +1,12 @@
 """Debug helper (GPU box): clock64() phase trace of CTA 0, chunk 4, of the chunk kernels on the bench workload."""
 import ctypes, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if "WKV6_B200_LIB" not in os.environ:      # the in-loop stamps live in the trace build (paper_accurate_fast_cheap_b200/build.py --trace)
+    _t = os.path.join(ROOT, "paper_accurate_fast_cheap_b200", "libwkv6_b200_trace.so")
+    if os.path.exists(_t):
+        os.environ["WKV6_B200_LIB"] = _t
+    else:
+        print("note: no trace build (python -m paper_accurate_fast_cheap_b200.build --trace): only the per-CTA timeline is recorded")
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import torch
 import paper_accurate_fast_cheap_b200 as pk
