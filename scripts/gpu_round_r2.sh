@@ -10,4 +10,5 @@ cat gpurun_out/bench_1gpu.json
 timeout 600 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
 cat gpurun_out/bench_ref.json
 timeout 900 bash scripts/gpu_prof_r2.sh > gpurun_out/prof_r2.log 2>&1; echo "prof rc=$?"
+timeout 300 python -m paper_accurate_fast_cheap_b200.build --trace > gpurun_out/build_trace.log 2>&1
 timeout 200 python scripts/trace_phases.py > gpurun_out/trace.txt 2>&1; grep "^bwd" gpurun_out/trace.txt | cut -c1-300
