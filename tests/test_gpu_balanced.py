@@ -78,3 +78,36 @@ def test_balanced_grid_against_oracle():
                          rev=rev, prec="f64")
         for x, r_ in zip(o[:6], ref[:6]):
             assert oracle.rel_err(x, r_) <= TOL[torch.bfloat16]
+
+
+def test_balanced_grid_under_cuda_graph_replay():
+    """A captured launch carries ONE epoch for all its replays: the consumer CTAs put every hand-over flag back to 0, so a
+    replay waits for its own producers instead of reading the previous replay's records.  Inputs change between replays."""
+    pk = _pk()
+    from paper_accurate_fast_cheap_b200 import ops
+    B, T, H = 16, 300, 8
+    a = _inputs(B, T, H, torch.bfloat16, seed=81)
+    b = _inputs(B, T, H, torch.bfloat16, seed=82, layer=7)
+    ga, gb = _cuda(a), _cuda(b)
+    f, r_ = tuple(ga[n] for n in "rkvwu"), tuple(gb[n] for n in "rkvwu")
+    ck = ops.checkpoint_buffer(ga["r"], 2)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):                    # warm-up outside the capture (lazy driver initialisation)
+        pk.bi_forward_raw(f, r_, ckpt=ck)
+        pk.bi_backward_raw(f, r_, ga["gy"], gb["gy"], ckpt=ck)
+    torch.cuda.current_stream().wait_stream(side)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        pk.bi_forward_raw(f, r_, ckpt=ck)
+        of, ob = pk.bi_backward_raw(f, r_, ga["gy"], gb["gy"], ckpt=ck)
+    for scale in (1.0, 0.5, 2.0):
+        ga["gy"].copy_((a["gy"].float() * scale).to(torch.bfloat16))
+        gb["gy"].copy_((b["gy"].float() * scale).to(torch.bfloat16))
+        g.replay()
+        torch.cuda.synchronize()
+        got = [t.clone() for t in of[:5] + ob[:5]]
+        pk.bi_forward_raw(f, r_, ckpt=ck)
+        ef, eb = pk.bi_backward_raw(f, r_, ga["gy"], gb["gy"], ckpt=ck)
+        for x, y in zip(got, ef[:5] + eb[:5]):
+            assert torch.equal(x, y)
