@@ -113,7 +113,8 @@ def _bwd_workspace_bytes(L, r, B, T, C, H, ndir, ckpt) -> int:
     """Without checkpoints: everything the backward needs.  With checkpoints: only the scratch of the time-segmented sweep
     (few, long sequences; `set_segmentation(False)` turns it off) or of the balanced persistent grid (more sequences than
     SMs; `set_balanced(False)`); 0 for every other shape."""
-    few_long = ndir * B * H <= 74        # the time-segmented sweep (else: the balanced persistent grid, more sequences than SMs)
+    # at most half as many sequences as SMs: the time-segmented sweep; more sequences than SMs: the balanced persistent grid
+    few_long = 2 * ndir * B * H <= torch.cuda.get_device_properties(r.device).multi_processor_count
     want_scratch = (_segmentation and T >= 2048) if few_long else _balanced
     if ckpt is None:
         nb = L.wkv6_b200_backward_workspace_bytes(_dtype_code(r), B, T, C, H, ndir)
