@@ -262,6 +262,13 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             }
         }
         }   // !so
+        // per-step decays 2^(-m) of the thread's four steps: the factors of steps 1..3 follow from those of the run's ends by
+        // products (10 ex2 per channel instead of 12: the MUFU pipe, 16 lanes per clock and SM, paces this phase)
+        float d[4][4];
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int e = 0; e < 4; e++) d[r][e] = ex2(-m[r][e]);
 #pragma unroll
         for (int e = 0; e < 4; e++) {   // inclusive sums over this thread's 4 steps
             m[1][e] += m[0][e];
@@ -280,24 +287,26 @@ __device__ __forceinline__ void lean_body(const Params& p, LeanSmem& sm, const D
             m[3][e] = x;                // inclusive total up to and including this thread's last step
         }
         if (rg == 3) *reinterpret_cast<float4*>(&sm.blocktot[c & 1][I][c0]) = make_float4(m[3][0], m[3][1], m[3][2], m[3][3]);
+        // fk[r] = 2^-(A+_p - a_I) >= 1 (inclusive), fr[r] = 2^(A_p - a_I) <= 1 (exclusive) of the thread's steps r = 0..3
+        float fk[4][4], fr[4][4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            fk[3][e] = ex2(m[3][e]);
+            fk[2][e] = fk[3][e] * d[3][e];
+            fk[1][e] = fk[2][e] * d[2][e];
+            fk[0][e] = fk[1][e] * d[1][e];
+            fr[0][e] = ex2(-excl[e]);
+            fr[1][e] = fr[0][e] * d[0][e];
+            fr[2][e] = fr[1][e] * d[1][e];
+            fr[3][e] = fr[2][e] * d[2][e];
+        }
 #pragma unroll
         for (int r = 0; r < 4; r++) {
-            float fr[4], fk[4];
-#pragma unroll
-            for (int e = 0; e < 4; e++) {
-                const float ain = r == 3 ? m[3][e] : excl[e] + m[r][e];         // -(A+_p - a_I) >= 0
-                fk[e] = ex2(ain);
-            }
-            ko2[r][0] = bmul2(kk[r][0], pack_bf16(fk[0], fk[1]));
-            ko2[r][1] = bmul2(kk[r][1], pack_bf16(fk[2], fk[3]));
+            ko2[r][0] = bmul2(kk[r][0], pack_bf16(fk[r][0], fk[r][1]));
+            ko2[r][1] = bmul2(kk[r][1], pack_bf16(fk[r][2], fk[r][3]));
             if (!so) {
-#pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const float aex = r ? excl[e] + m[r - 1][e] : excl[e];      // -(A_p  - a_I) >= 0
-                    fr[e] = ex2(-aex);
-                }
-                ro2[r][0] = bmul2(rr[r][0], pack_bf16(fr[0], fr[1]));
-                ro2[r][1] = bmul2(rr[r][1], pack_bf16(fr[2], fr[3]));
+                ro2[r][0] = bmul2(rr[r][0], pack_bf16(fr[r][0], fr[r][1]));
+                ro2[r][1] = bmul2(rr[r][1], pack_bf16(fr[r][2], fr[r][3]));
                 sts64(roff_u32 + offs[r], ro2[r][0], ro2[r][1]);
                 sts64(kt_u32 + vb_own + offs[r], ko2[r][0], ko2[r][1]);   // Ktil(own): operand of G1 only
             }
