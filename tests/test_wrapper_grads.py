@@ -171,10 +171,16 @@ def test_graphed_training_matches_eager_with_direction_dropout():
     outcomes = set()
     for (o1, gx1, gp1), (o2, gx2, gp2) in zip(eager, graphed):
         assert torch.equal(o1, o2) and torch.equal(gx1, gx2)
-        for a, b in zip(gp1, gp2):
+        for (name, _), a, b in zip(m.named_parameters(), gp1, gp2):
             assert (a is None) == (b is None)
-            if a is not None:
-                assert torch.equal(a, b)
+            if a is None:
+                continue
+            if "time_maa" in name:
+                # the token-shift mix vectors' gradients are column sums accumulated with fp32 atomics across CTAs
+                # (csrc/wkv6_tmix.cu): the order of the additions is not fixed, so two runs may differ in the last bf16 bit
+                assert (a.float() - b.float()).abs().max() <= 2.0 ** -7 * a.float().abs().max(), name
+            else:
+                assert torch.equal(a, b), name
         n_f = sum(g is not None for (n, _), g in zip(m.named_parameters(), gp1) if n.startswith("rwkv_wrapper_forward"))
         n_b = sum(g is not None for (n, _), g in zip(m.named_parameters(), gp1) if n.startswith("rwkv_wrapper_backward"))
         outcomes.add((n_f > 0, n_b > 0))
