@@ -256,6 +256,7 @@ def run_b200(args):
     import torch.distributed as dist
     import paper_accurate_fast_cheap_b200 as pk
     from paper_accurate_fast_cheap_b200 import _lib
+    from paper_accurate_fast_cheap_b200.sharding import max_over_ranks, shard_rows
 
     legs = set() if args.legs == "none" else set(x for x in args.legs.split(",") if x)
     rank = int(os.environ.get("RANK", "0"))
@@ -311,11 +312,8 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def allmax(ms):
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    def allmax(ms):                      # a multi-GPU number is the MAX over ranks of the device-measured time
+        return max_over_ranks(ms, dev)
 
     def region(fn, reps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -571,7 +569,8 @@ def run_b200(args):
     def leg_longform():
         if world > 8:
             return None
-        LT, LB = 30000, max(1, 8 // world)
+        _lb, _le = shard_rows(8, rank, world)          # configs[2]: 8 utterances sharded over the ranks
+        LT, LB = 30000, max(1, _le - _lb)
         gl = torch.Generator(device=dev).manual_seed(777 + rank)
         lsets = []
         for _ in range(2):
