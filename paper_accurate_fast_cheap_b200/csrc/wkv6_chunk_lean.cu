@@ -608,17 +608,21 @@ __global__ void __launch_bounds__(256) wkv6_seg_scan_kernel(const __grid_constan
 // One-pass time-segmented forward, second kernel: y of every chunk outside the first segment was computed from S = 0 at the
 // start of its segment; the state carried into the segment contributes  y_p += sum_j r_p[j] 2^(A_p[j]) Dp[j] S_start[.][j],
 // Dp = decay from the start of the segment to the start of the chunk (written per chunk by the first kernel), S_start from
-// the segment scan.  One CTA per (sequence, chunk), no dependence between CTAs: r, w and y tiles by TMA, the r 2^(A_p) Dp tile
-// rebuilt from r and w (decays, in-block cumulative sums -- the R side of the main kernel's tile building), one M64 N64 K64
-// MMA group against the bf16 copy of S_start, y tile updated in shared memory and stored back.  41 KB, 64 TMEM columns.
+// the segment scan.  One CTA per (sequence, segment, piece of the segment): the bf16 copy of S_start is built ONCE and the
+// CTA walks its run of chunks with the r, w and y tiles of the next two chunks in flight (TMA, two stages); per chunk: the
+// r 2^(A_p) Dp tile rebuilt from r and w (decays, in-block cumulative sums -- the R side of the main kernel's tile building),
+// one M64 N64 K64 MMA group against S_start, y tile updated in shared memory and stored back.  66 KB, 64 TMEM columns: three
+// CTAs per SM.  (The first version ran one CTA per chunk -- barrier init, TMEM allocation, a 16 KB state load and a serial
+// load -> compute -> store chain for 24 KB of traffic each: 75 us per configs[2] block at one utterance per GPU, twice the
+// time of its bytes.)
 struct CorrSmem {
-    alignas(1024) uint8_t raw_r[CL * 128];
-    alignas(1024) uint8_t raw_w[CL * 128];
-    alignas(1024) uint8_t y[CL * 128];
+    alignas(1024) uint8_t raw_r[2][CL * 128];
+    alignas(1024) uint8_t raw_w[2][CL * 128];
+    alignas(1024) uint8_t y[2][CL * 128];
     alignas(1024) uint8_t rc[CL * 128];      // r 2^(A_p) Dp, K-major [p][j]
     alignas(1024) uint8_t sp[N * 128];       // S_start^T [j][i] bf16 (MN-major B operand, as in the main kernel)
     float blocktot[4][N];
-    alignas(8) uint64_t bar_in, bar_m;
+    alignas(8) uint64_t bar_in[2], bar_m;
     uint32_t tmem_base;
 };
 
@@ -628,29 +632,40 @@ __global__ void __launch_bounds__(256) wkv6_fwd_corr_kernel(const __grid_constan
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     // corr_first: the first chunk that needs the correction -- seg_chunks (the first segment starts from S_0 = 0 and is
-    // already right) or 0 (a caller-supplied S_0 is carried into the first segment like any other start state)
-    const int BH = p.B * p.H, ntot = (p.T + CL - 1) / CL, per_seq = ntot - p.corr_first;
-    const int seq = blockIdx.x / per_seq, c = p.corr_first + (blockIdx.x - seq * per_seq);   // chunk in processing order
-    const int seg = c / p.seg_chunks;
+    // already right) or 0 (a caller-supplied S_0 is carried into the first segment like any other start state).
+    // blockIdx = ((sequence * segments) + segment) * corr_pp + piece; a piece is corr_pc consecutive chunks of the segment.
+    const int BH = p.B * p.H, ntot = (p.T + CL - 1) / CL;
+    const int seg_first = p.corr_first / p.seg_chunks, nsegc = p.nseg - seg_first;
+    const int piece = blockIdx.x % p.corr_pp, ss = blockIdx.x / p.corr_pp;
+    const int seq = ss / nsegc, seg = seg_first + (ss - seq * nsegc);
+    const int cfirst = seg * p.seg_chunks + piece * p.corr_pc;                              // chunks in processing order
+    const int cend = min(min(cfirst + p.corr_pc, (seg + 1) * p.seg_chunks), ntot);
+    const int n = cend - cfirst;
+    if (n <= 0) return;                                                                    // (CTA-uniform)
     const int ds = seq / BH, bh = seq - ds * BH, b = bh / p.H, h = bh - b * p.H;
     const DirArgs& D = p.d[ds];
     const bool rev = D.reverse != 0;
-    const int q = rev ? ntot - 1 - c : c, t0 = q * CL;
+    auto issue = [&](int i) {                  // thread 0: r, w, y tiles of the CTA's chunk i into stage i & 1
+        const int c = cfirst + i, t0 = (rev ? ntot - 1 - c : c) * CL, st = i & 1;
+        mbar_arrive_expect_tx(&sm.bar_in[st], 3u * CL * 128);
+        tma_load_3d(sm.raw_r[st], &D.mr, &sm.bar_in[st], h * N, t0, b);
+        tma_load_3d(sm.raw_w[st], &D.mw, &sm.bar_in[st], h * N, t0, b);
+        tma_load_3d(sm.y[st], &D.my, &sm.bar_in[st], h * N, t0, b);
+    };
     if (tid == 0) {
-        mbar_init(&sm.bar_in, 1);
+        mbar_init(&sm.bar_in[0], 1);
+        mbar_init(&sm.bar_in[1], 1);
         mbar_init(&sm.bar_m, 1);
         fence_barrier_init();
         fence_proxy_async();
-        mbar_arrive_expect_tx(&sm.bar_in, 3u * CL * 128);
-        tma_load_3d(sm.raw_r, &D.mr, &sm.bar_in, h * N, t0, b);
-        tma_load_3d(sm.raw_w, &D.mw, &sm.bar_in, h * N, t0, b);
-        tma_load_3d(sm.y, &D.my, &sm.bar_in, h * N, t0, b);
+        issue(0);
+        if (n > 1) issue(1);
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    // S_start [i][j] fp32 -> bf16 tile [j][i] (16 elements per thread: i = tid >> 2, j = 16 * (tid & 3) ..)
+    // S_start [i][j] fp32 -> bf16 tile [j][i] (16 elements per thread: i = tid >> 2, j = 16 * (tid & 3) ..), once per CTA
     {
         const float* S = p.seg_state + ((size_t)seq * p.nseg + seg) * N * N;
         const int i = tid >> 2, j0 = 16 * (tid & 3);
@@ -673,107 +688,121 @@ __global__ void __launch_bounds__(256) wkv6_fwd_corr_kernel(const __grid_constan
     const int cq = lane & 7, rg = lane >> 3;
     const int c0 = 32 * ch + 4 * cq;
     const int coff = (c0 & 7) * 2, cchunk = c0 >> 3;
-    float pre[4];
-    {
-        const float4 f = *reinterpret_cast<const float4*>(p.seg_prefix + ((size_t)seq * ntot + c) * N + c0);
-        pre[0] = f.x; pre[1] = f.y; pre[2] = f.z; pre[3] = f.w;
-    }
-    __syncthreads();   // the barriers thread 0 initialised are visible before anybody waits on them
-    mbar_wait(&sm.bar_in, 0);
-    float ro[4][4];
-    {
-        float l2[4][4];
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-            const int pos = 16 * I + 4 * rg + r;
-            const int row = rev ? 63 - pos : pos;
-            const int off = sw_chunk(row, cchunk) + coff;
-            float w4[4];
-            ld4bf(sm.raw_r + off, ro[r]);
-            ld4bf(sm.raw_w + off, w4);
-            const bool valid = t0 + row < p.T;
-#pragma unroll
-            for (int e = 0; e < 4; e++) {
-                const float x = ex2(w4[e] * kLog2e);
-                l2[r][e] = valid ? fmaxf(-x * kLog2e, -kClampL2) : 0.f;
-            }
-        }
-#pragma unroll
-        for (int e = 0; e < 4; e++) {
-            l2[1][e] += l2[0][e];
-            l2[2][e] += l2[1][e];
-            l2[3][e] += l2[2][e];
-        }
-#pragma unroll
-        for (int e = 0; e < 4; e++) {
-            float x = l2[3][e];
-            float y = __shfl_up_sync(0xffffffffu, x, 8);
-            if (rg >= 1) x += y;
-            y = __shfl_up_sync(0xffffffffu, x, 16);
-            if (rg >= 2) x += y;
-            const float excl = x - l2[3][e];
-            if (rg == 3) sm.blocktot[I][c0 + e] = x;
-#pragma unroll
-            for (int r = 0; r < 4; r++) ro[r][e] *= ex2(excl + (r ? l2[r - 1][e] : 0.f));
-        }
-    }
-    __syncthreads();   // blocktot visible; tmem_base visible
-    {
-        float fst[4];
-#pragma unroll
-        for (int e = 0; e < 4; e++) {
-            float s_ = 0.f;
-#pragma unroll
-            for (int m = 0; m < 4; m++)
-                if (m < I) s_ += sm.blocktot[m][c0 + e];
-            fst[e] = ex2(s_) * pre[e];
-        }
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-            const int pos = 16 * I + 4 * rg + r;
-            const int row = rev ? 63 - pos : pos;
-            float x4[4];
-#pragma unroll
-            for (int e = 0; e < 4; e++) x4[e] = ro[r][e] * fst[e];
-            st4bf(sm.rc + sw_chunk(row, cchunk) + coff, x4);
-        }
-    }
     fence_proxy_async();
     tc_fence_before();
-    __syncthreads();
+    __syncthreads();   // barriers, tmem_base and the S_start tile are visible
     tc_fence_after();
     const uint32_t tY = __shfl_sync(0xffffffffu, sm.tmem_base, 0);
-    if (warp == 0 && elect_one()) {
-        const uint64_t dk_rc = desc_k(smem_u32(sm.rc)), dm_sp = desc_mn(smem_u32(sm.sp));
-        constexpr uint32_t ID = umma_idesc(0, 1, 64, 64);
+    const uint64_t dk_rc = desc_k(smem_u32(sm.rc)), dm_sp = desc_mn(smem_u32(sm.sp));
+    constexpr uint32_t ID = umma_idesc(0, 1, 64, 64);
+
+    for (int i = 0; i < n; i++) {
+        const int c = cfirst + i, st = i & 1;
+        const int t0 = (rev ? ntot - 1 - c : c) * CL;
+        float pre[4];
+        {
+            const float4 f = *reinterpret_cast<const float4*>(p.seg_prefix + ((size_t)seq * ntot + c) * N + c0);
+            pre[0] = f.x; pre[1] = f.y; pre[2] = f.z; pre[3] = f.w;
+        }
+        mbar_wait(&sm.bar_in[st], (i >> 1) & 1);
+        float ro[4][4];
+        {
+            float l2[4][4];
 #pragma unroll
-        for (int ks = 0; ks < 4; ks++) umma(tY, dk_rc + (uint64_t)((ks * 32) >> 4), dm_sp + (uint64_t)((ks * 2048) >> 4), ID, ks > 0);
-        umma_commit(&sm.bar_m);
-    }
-    __syncwarp();
-    mbar_wait(&sm.bar_m, 0);
-    tc_fence_after();
-    {
-        float x[16];
-        tmem_ld_16x32(tY + lane_field + 32 * half, x);
+            for (int r = 0; r < 4; r++) {
+                const int pos = 16 * I + 4 * rg + r;
+                const int row = rev ? 63 - pos : pos;
+                const int off = sw_chunk(row, cchunk) + coff;
+                float w4[4];
+                ld4bf(sm.raw_r[st] + off, ro[r]);
+                ld4bf(sm.raw_w[st] + off, w4);
+                const bool valid = t0 + row < p.T;
 #pragma unroll
-        for (int rep = 0; rep < 4; rep++)
-#pragma unroll
-            for (int hh = 0; hh < 2; hh++) {
-                const int col = fcol + 8 * rep;
-                uint32_t* wp = reinterpret_cast<uint32_t*>(sm.y + sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2);
-                const uint32_t old = *wp;
-                *wp = pack_bf16(__uint_as_float(old << 16) + x[4 * rep + 2 * hh], __uint_as_float(old & 0xffff0000u) + x[4 * rep + 2 * hh + 1]);
+                for (int e = 0; e < 4; e++) {
+                    const float x = ex2(w4[e] * kLog2e);
+                    l2[r][e] = valid ? fmaxf(-x * kLog2e, -kClampL2) : 0.f;
+                }
             }
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                l2[1][e] += l2[0][e];
+                l2[2][e] += l2[1][e];
+                l2[3][e] += l2[2][e];
+            }
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                float x = l2[3][e];
+                float y = __shfl_up_sync(0xffffffffu, x, 8);
+                if (rg >= 1) x += y;
+                y = __shfl_up_sync(0xffffffffu, x, 16);
+                if (rg >= 2) x += y;
+                const float excl = x - l2[3][e];
+                if (rg == 3) sm.blocktot[I][c0 + e] = x;
+#pragma unroll
+                for (int r = 0; r < 4; r++) ro[r][e] *= ex2(excl + (r ? l2[r - 1][e] : 0.f));
+            }
+        }
+        __syncthreads();   // S1: blocktot visible
+        {
+            float fst[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                float s_ = 0.f;
+#pragma unroll
+                for (int m = 0; m < 4; m++)
+                    if (m < I) s_ += sm.blocktot[m][c0 + e];
+                fst[e] = ex2(s_) * pre[e];
+            }
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int pos = 16 * I + 4 * rg + r;
+                const int row = rev ? 63 - pos : pos;
+                float x4[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) x4[e] = ro[r][e] * fst[e];
+                st4bf(sm.rc + sw_chunk(row, cchunk) + coff, x4);
+            }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();   // S2: the operand tile is complete
+        tc_fence_after();
+        if (warp == 0 && elect_one()) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) umma(tY, dk_rc + (uint64_t)((ks * 32) >> 4), dm_sp + (uint64_t)((ks * 2048) >> 4), ID, ks > 0);
+            umma_commit(&sm.bar_m);
+        }
+        __syncwarp();
+        mbar_wait(&sm.bar_m, i & 1);
+        tc_fence_after();
+        {
+            float x[16];
+            tmem_ld_16x32(tY + lane_field + 32 * half, x);
+#pragma unroll
+            for (int rep = 0; rep < 4; rep++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) {
+                    const int col = fcol + 8 * rep;
+                    uint32_t* wp = reinterpret_cast<uint32_t*>(sm.y[st] + sw_chunk(frow + 8 * hh, col >> 3) + (col & 7) * 2);
+                    const uint32_t old = *wp;
+                    *wp = pack_bf16(__uint_as_float(old << 16) + x[4 * rep + 2 * hh], __uint_as_float(old & 0xffff0000u) + x[4 * rep + 2 * hh + 1]);
+                }
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();   // S3: y tile complete; TMEM reads, blocktot and operand-tile reads of this chunk done
+        if (tid == 0) {
+            tma_store_3d(&D.my, sm.y[st], h * N, t0, b);
+            tma_store_commit();
+            if (i + 2 < n) {               // refill this stage: the store must have read the y tile first
+                tma_store_wait_read<0>();
+                issue(i + 2);
+            }
+        }
     }
-    fence_proxy_async();
+    if (tid == 0) tma_store_wait<0>();
     tc_fence_before();
     __syncthreads();
-    if (tid == 0) {
-        tma_store_3d(&D.my, sm.y, h * N, t0, b);
-        tma_store_commit();
-        tma_store_wait<0>();
-    }
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tY) : "memory");
 }
 
@@ -853,7 +882,22 @@ int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_by
         qc.corr_first = q.seg_chunks;
         for (int d = 0; d < q.ndir; d++)
             if (q.d[d].s0) qc.corr_first = 0;
-        wkv6_fwd_corr_kernel<<<dim3(q.ndir * q.B * q.H * (ntot - qc.corr_first)), dim3(256), smem, st>>>(qc);
+        // pieces per segment: enough CTAs for three per SM, the fewest (waves x chunks per CTA), at least 4 chunks per CTA
+        // where the segments allow it (the S_start tile is built once per CTA)
+        const int nsegc = q.nseg - qc.corr_first / q.seg_chunks, nss = q.ndir * q.B * q.H * nsegc;
+        int best_pp = 1;
+        long best_cost = -1;
+        for (int pp = 1; pp <= 16 && pp <= q.seg_chunks; pp++) {
+            const int pc = (q.seg_chunks + pp - 1) / pp;
+            if (pp > 1 && pc < 4) break;
+            const long waves = ((long)nss * pp + 3 * 148 - 1) / (3 * 148);
+            const long cost = waves * (pc + 1);                  // + 1: the CTA's prologue
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_pp = pp; }
+        }
+        qc.corr_pp = best_pp;
+        qc.corr_pc = (q.seg_chunks + best_pp - 1) / best_pp;
+        (void)ntot;
+        wkv6_fwd_corr_kernel<<<dim3(nss * best_pp), dim3(256), smem, st>>>(qc);
         count_launch(1);
         return (int)cudaGetLastError();
     }

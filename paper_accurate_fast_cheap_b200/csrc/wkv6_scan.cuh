@@ -42,6 +42,7 @@ struct Params {
     float* seg_decay;                     // [ndir][B*H][nseg][64 j]: product of the per-step decays of the segment
     float* seg_gu;                        // time-segmented backward: [ndir][B*H][nseg][64] partial gu of every segment
     int corr_first;                       // one-pass segmented forward: first chunk wkv6_fwd_corr_kernel touches
+    int corr_pp, corr_pc;                 // its CTAs: pieces per segment, chunks per piece
     float* seg_prefix;                    // one-pass segmented forward: [ndir][B*H][chunks][64] decay from segment start to chunk start
     // balanced persistent backward (wkv6_chunk_bwd.cu): CTAs per direction (0: off), hand-over records, flag value of the launch
     int bal_ncta;
