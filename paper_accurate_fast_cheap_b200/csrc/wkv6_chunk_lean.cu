@@ -588,6 +588,8 @@ __global__ void __launch_bounds__(256) wkv6_seg_scan_kernel(const __grid_constan
     const DirArgs& D = p.d[ds];
     float* st = p.seg_state + (size_t)seq * p.nseg * N * N + e;
     const float* dec = p.seg_decay + (size_t)seq * p.nseg * N + j;
+    pdl_launch_dependents();   // programmatic dependent launch (wkv6_common.cuh): the correction kernel's prologue may start
+    pdl_wait();                // pass 1 has completed and its writes are visible
     float dS[kMaxSeg], dk[kMaxSeg];
 #pragma unroll
     for (int s = 0; s < kMaxSeg; s++)
@@ -641,6 +643,7 @@ __global__ void __launch_bounds__(256) wkv6_fwd_corr_kernel(const __grid_constan
     const int cfirst = seg * p.seg_chunks + piece * p.corr_pc;                              // chunks in processing order
     const int cend = min(min(cfirst + p.corr_pc, (seg + 1) * p.seg_chunks), ntot);
     const int n = cend - cfirst;
+    pdl_launch_dependents();                                                               // (the next block's first kernel)
     if (n <= 0) return;                                                                    // (CTA-uniform)
     const int ds = seq / BH, bh = seq - ds * BH, b = bh / p.H, h = bh - b * p.H;
     const DirArgs& D = p.d[ds];
@@ -658,6 +661,7 @@ __global__ void __launch_bounds__(256) wkv6_fwd_corr_kernel(const __grid_constan
         mbar_init(&sm.bar_m, 1);
         fence_barrier_init();
         fence_proxy_async();
+        pdl_wait();            // the segment scan (and with it the first kernel) has completed
         issue(0);
         if (n > 1) issue(1);
     }
@@ -665,6 +669,7 @@ __global__ void __launch_bounds__(256) wkv6_fwd_corr_kernel(const __grid_constan
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_u32(&sm.tmem_base)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    pdl_wait();
     // S_start [i][j] fp32 -> bf16 tile [j][i] (16 elements per thread: i = tid >> 2, j = 16 * (tid & 3) ..), once per CTA
     {
         const float* S = p.seg_state + ((size_t)seq * p.nseg + seg) * N * N;
@@ -848,9 +853,9 @@ size_t segment_scratch_bytes(const Params& p, int min_seg) {
 
 int launch_seg_scan(const Params& q, cudaStream_t st) {
     if (q.nseg > kMaxSeg) return (int)cudaErrorInvalidValue;
-    wkv6_seg_scan_kernel<<<dim3(q.ndir * q.B * q.H * 16), dim3(256), 0, st>>>(q);
+    const cudaError_t e = launch_pdl(wkv6_seg_scan_kernel, dim3(q.ndir * q.B * q.H * 16), dim3(256), 0, st, q);
     count_launch(1);
-    return (int)cudaGetLastError();
+    return e != cudaSuccess ? (int)e : (int)cudaGetLastError();
 }
 
 // Segmented forward: pass 1, scan, pass 2 on the caller's scratch buffer.  Returns -1 when the launch does not qualify.
@@ -897,9 +902,9 @@ int launch_fwd_chunk_segmented(const Params& p, void* scratch, size_t scratch_by
         qc.corr_pp = best_pp;
         qc.corr_pc = (q.seg_chunks + best_pp - 1) / best_pp;
         (void)ntot;
-        wkv6_fwd_corr_kernel<<<dim3(nss * best_pp), dim3(256), smem, st>>>(qc);
+        ce = launch_pdl(wkv6_fwd_corr_kernel, dim3(nss * best_pp), dim3(256), smem, st, qc);
         count_launch(1);
-        return (int)cudaGetLastError();
+        return ce != cudaSuccess ? (int)ce : (int)cudaGetLastError();
     }
     q.seg_mode = 1;
     int e = launch_fwd_chunk(q, st);
